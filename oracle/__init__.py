@@ -1,0 +1,18 @@
+"""CPU oracle for the TopoFlow 3.5 D8 + channel-routing hot path.
+
+TEST INFRASTRUCTURE ONLY.  This package is a NumPy restatement of the
+reference's algorithm (peckhams/topoflow_old, topoflow/components/
+channels_*.py, d8_base.py, d8_global.py).  It exists so the CUDA path can be
+checked against it.  Only ``tests/``, ``__graft_entry__.smoke()`` and the
+``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` may import it; the
+product package ``topoflow_old_b200`` never does.
+
+Parity status: PINNED.
+  * D8 codes      : bit-exact vs the reference's shipped Treynor_flow.rtg
+  * D8 area       : bit-exact (float32) vs Treynor_area.rtg
+  * tie-break LUT : equals the RT3 16x16 table, sum 10161
+                    (components/tests/test_d8_base_UNFINISHED.py:101-125)
+  * routing       : reproduces the shipped Test_Plane_Canal hydrographs
+                    (examples/Test_Plane_Canal/00_Output_Files/Case1_0D-*.txt)
+see tests/test_oracle_*.py.
+"""
