@@ -1,0 +1,369 @@
+#!/usr/bin/env python
+"""Headline benchmark: grid cell-updates/s of the fp64 channel-routing step.
+
+    python bench.py --gpus 1 --steps 20 --warmup 5
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference ...      (the CPU path, NumPy, 1 core)
+
+Workload (BASELINE.json north_star): kinematic-wave, Manning friction, fp64
+state on a synthetic fractal DEM of --size x --size cells per GPU (default
+16384 x 16384), uniform rain pulse, D8 grid built on the GPU first.  With N
+GPUs the grid is N strips of --size rows stacked north to south (weak
+scaling), one halo row of Q exchanged per step over NCCL.
+
+One JSON line on stdout (rank 0); everything else goes to stderr.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+ALGO_BYTES = {'kinematic': 97.0, 'diffusive': 113.0, 'dynamic': 129.0}
+WAVE_ID = {'kinematic': 0, 'diffusive': 1, 'dynamic': 2}
+DT = {'kinematic': 2.0, 'diffusive': 2.0, 'dynamic': 0.5}
+CELL = 30.0
+RAIN_MPS = 50.0 / 3.6e6            # 50 mm/h uniform rain pulse
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        return float(json.load(open(p))['hbm_gbs']), 'measured (MEASURED_PEAKS.json)'
+    return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+# ---------------------------------------------------------------------------
+# inputs
+# ---------------------------------------------------------------------------
+def synth_inputs(nx, global_ny, row0, nrows, seed=20170226):
+    """DEM strip (+ its halo rows) and the float32 parameter grids, as the
+    reference would read them from RTG files."""
+    from concurrent.futures import ThreadPoolExecutor
+    from topoflow_old_b200.utils import synth
+    lo, hi = max(row0 - 1, 0), min(row0 + nrows + 1, global_ny)
+    chunks = [(a, min(a + 512, hi)) for a in range(lo, hi, 512)]
+    with ThreadPoolExecutor(max_workers=min(32, os.cpu_count() or 1)) as ex:
+        parts = list(ex.map(lambda ab: synth.fractal_dem(nx, global_ny, row0=ab[0], nrows=ab[1] - ab[0],
+                                                         seed=seed, cell=CELL, roughness=8.0), chunks))
+    dem = np.concatenate(parts, axis=0)
+    north = dem[0] if row0 > 0 else None
+    south = dem[-1] if row0 + nrows < global_ny else None
+    dem = dem[(row0 - lo):(row0 - lo) + nrows]
+    nval = synth.uniform_field(nx, global_ny, 0.03, 0.15, row0=row0, nrows=nrows, seed=seed + 3)
+    width = synth.uniform_field(nx, global_ny, 1.0, 6.0, row0=row0, nrows=nrows, seed=seed + 1)
+    angle = synth.class_field(nx, global_ny, [20.0, 30.0, 45.0], row0=row0, nrows=nrows,
+                              seed=seed + 2, block=64)
+    return dem, north, south, nval, width, angle
+
+
+def build_strip(args, rank, nranks, device, unique_id=None):
+    """D8 grid and routing state of this rank's strip, ready to step."""
+    from topoflow_old_b200 import _lib as L
+    from topoflow_old_b200.engine import Strip
+    from topoflow_old_b200.routing import setup_channels
+    from topoflow_old_b200.utils import synth
+    nx, ny = args.size, args.size
+    global_ny = ny * nranks
+    row0 = rank * ny
+    t0 = time.time()
+    dem, north, south, nval, width, angle = synth_inputs(nx, global_ny, row0, ny)
+    log('[rank %d] synthetic inputs %.1fs' % (rank, time.time() - t0))
+    s = Strip(nx, ny, device=device)
+    if nranks > 1:
+        s.set_strip(row0, global_ny, rank > 0, rank < nranks - 1)
+        s.comm_init(rank, nranks, unique_id)
+    dx = np.full(ny, CELL, dtype=np.float32)
+    dd = np.full(ny, np.float32(np.sqrt(np.float64(CELL) ** 2 * 2)), dtype=np.float32)
+    t0 = time.time()
+    stats = s.d8_build(dem, dx, dx, dd)
+    log('[rank %d] D8 build %.2fs %s' % (rank, time.time() - t0, stats))
+    code = s.d8_get(L.D8_CODE)
+    ds = s.d8_get(L.D8_DS)
+    dw = s.d8_get(L.D8_DW)
+    slope = synth.d8_slope(dem, code, ds, north=north, south=south)
+    del dem
+    width = np.float64(width)
+    width[width == 0] = dw[width == 0]                       # channels_base.py:2182-2183
+    angle = np.float64(angle)
+    angle *= np.pi / 180.0                                   # :2191
+    outlets = [(ny // 2, nx // 2), (ny - 2, nx - 2)]
+    t0 = time.time()
+    setup_channels(s, WAVE_ID[args.wave], L.MANNING, DT[args.wave], CELL * CELL, np.float64(slope),
+                   width, angle, np.float64(nval), sinu=1.0, d0=0.0, outlets=outlets,
+                   allow_packed=not args.generic, ds=ds)
+    log('[rank %d] routing setup %.1fs' % (rank, time.time() - t0))
+    s.set_R(RAIN_MPS)
+    return s
+
+
+# ---------------------------------------------------------------------------
+# clocks during the timed region
+# ---------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, device):
+        super().__init__(daemon=True)
+        self.device, self.rows, self.stop_flag = device, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(['nvidia-smi', '-i', str(self.device), '--query-gpu=' + self.Q,
+                                      '--format=csv,noheader,nounits'], capture_output=True,
+                                     text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(',')])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        self.stop_flag = True
+        if not self.rows:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i] == 'Active' for r in self.rows)]
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': float(self.rows[0][1]),
+                'reasons': reasons, 'samples': len(sm)}
+
+
+# ---------------------------------------------------------------------------
+# CPU path (the oracle: NumPy restatement of the reference, one core)
+# ---------------------------------------------------------------------------
+def cpu_path(wave, size, steps, warmup):
+    """cell-updates/s of the reference algorithm on the host, on a size x size
+    sample of the same synthetic workload."""
+    from oracle import channels as och
+    from oracle import d8 as od8
+    from topoflow_old_b200.utils import synth
+    dem = synth.fractal_dem(size, size, cell=CELL, roughness=8.0)
+    b = od8.build(dem, CELL, CELL)
+    slope = synth.d8_slope(dem, b['d8_grid'], b['ds'])
+    nval = synth.uniform_field(size, size, 0.03, 0.15, seed=20170229)
+    width = synth.uniform_field(size, size, 1.0, 6.0, seed=20170227)
+    angle = synth.class_field(size, size, [20.0, 30.0, 45.0], seed=20170228, block=64)
+    inp = och.prepare_inputs(b, slope, width, angle, nval=nval)
+    ch = och.ChannelsOracle(b, WAVE_ID[wave], dt=DT[wave], da=np.float64(CELL * CELL),
+                            slope=inp['slope'], width=inp['width'], angle=inp['angle'],
+                            nval=inp['nval'], outlet_ID=(size // 2, size // 2))
+    ch.P_rain = och.scalar(RAIN_MPS)
+    for _ in range(warmup):
+        ch.update()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ch.update()
+    el = time.perf_counter() - t0
+    return size * size * steps / el, el
+
+
+# ---------------------------------------------------------------------------
+# distributed plumbing (torch.distributed only carries the NCCL id, the
+# barriers and the max-over-ranks of the timings)
+# ---------------------------------------------------------------------------
+class Dist(object):
+    def __init__(self, n_gpus):
+        self.rank = int(os.environ.get('RANK', '0'))
+        self.world = int(os.environ.get('WORLD_SIZE', '1'))
+        self.local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+        self.torch = None
+        if self.world > 1:
+            import torch
+            import torch.distributed as dist
+            self.torch, self.dist = torch, dist
+            os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+            torch.cuda.set_device(self.local_rank)
+            dist.init_process_group(backend='nccl', device_id=torch.device('cuda', self.local_rank))
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+            self.torch.cuda.synchronize()
+
+    def bcast_bytes(self, arr):
+        if self.world == 1:
+            return arr
+        t = self.torch.from_numpy(arr.copy()).cuda()
+        self.dist.broadcast(t, src=0)
+        return t.cpu().numpy()
+
+    def max(self, v):
+        if self.world == 1:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device='cuda')
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum(self, v):
+        if self.world == 1:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device='cuda')
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def close(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+def run_gpu(args):
+    from topoflow_old_b200.engine import Strip
+    D = Dist(args.gpus)
+    if D.world != args.gpus:
+        log('warning: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE' % (args.gpus, D.world))
+    uid = None
+    if D.world > 1:
+        uid = Strip.comm_unique_id() if D.rank == 0 else np.zeros(128, dtype=np.uint8)
+        uid = D.bcast_bytes(uid)
+    s = build_strip(args, D.rank, D.world, D.local_rank, uid)
+    cells = float(args.size) * args.size              # per GPU
+    K, W = args.steps, max(args.warmup, 0)
+
+    # ---- device-resident throughput ("value") -------------------------------
+    s.step_async(W)
+    s.sync()
+    s.timing()
+    D.barrier()
+    sampler = ClockSampler(D.local_rank)
+    sampler.start()
+    t0 = time.perf_counter()
+    s.step_async(K)
+    ms_dev, n_steps, launches, layout_bytes = s.timing()      # CUDA events on the stream
+    s.sync()
+    D.barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.summary()
+    ms = D.max(ms_dev)
+    value = cells * D.world * K / (ms * 1e-3)
+
+    # ---- end to end: one public call per step, host buffers -------------------
+    D.barrier()
+    t0 = time.perf_counter()
+    Ke = K
+    for _ in range(Ke):
+        s.set_R(RAIN_MPS, want_sum=False)             # this step's forcing (6 scalars -> R)
+        taps, _, bad = s.step(1)                      # outlet Q,u,d,f + bad-value flags back
+    D.barrier()
+    e2e_s = D.max(time.perf_counter() - t0)
+    e2e = cells * D.world * Ke / e2e_s
+    assert bad[0] == -1 and bad[1] == -1, 'bad depth / velocity flagged: %s' % bad
+    s.timing()
+
+    line = None
+    peak, peak_src = peaks()
+    if D.rank == 0:
+        kernel_ms = ms_dev / K                        # one fused kernel per step (kinematic)
+        achieved = ALGO_BYTES[args.wave] * cells / (kernel_ms * 1e-3) / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, 'profiles', 'traffic_%s.json' % args.wave)
+        if os.path.exists(tp):
+            tj = json.load(open(tp))
+            if tj.get('size') == args.size:
+                traffic = tj.get('dram_bytes_per_launch')
+        line = {
+            'metric': 'grid cell-updates/sec (fp64 routing step)', 'value': value,
+            'unit': 'cell-updates/s', 'n_gpus': D.world, 'steps': K, 'warmup': W,
+            'ms_per_step': ms / K, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+            'config': {'workload': 'synthetic %dx%d fractal DEM per GPU, %s-wave channels, Manning, '
+                                   'uniform rain pulse, D8 built on GPU' % (args.size, args.size, args.wave),
+                       'grid_per_gpu': [args.size, args.size], 'wave': args.wave,
+                       'layout': 'generic-f64' if args.generic else 'packed (exact f32 params + angle table)',
+                       'l2_policy': 'inputs larger than L2 (%.1f GB touched per step)' % (layout_bytes * cells / 1e9),
+                       'parallelism': 'row strips x%d, 1 halo row of Q per step over NCCL' % D.world},
+            'e2e': {'value': e2e, 'unit': 'cell-updates/s', 'h2d_bytes_per_step': 8 * 6,
+                    'd2h_bytes_per_step': 8 * 4 * s.n_outlets + 16},
+            'gpu_launches': int(launches),
+            'clocks': clocks,
+            'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                         'frac': achieved / peak, 'traffic': traffic,
+                         'peak_source': peak_src,
+                         'algorithmic_bytes_per_cell': ALGO_BYTES[args.wave],
+                         'layout_bytes_per_cell': layout_bytes,
+                         'kernel_ms': kernel_ms},
+            'wall_ms_timed_region': wall_ms,
+        }
+        if not args.no_cpu:
+            v, el = cpu_path(args.wave, args.cpu_size, args.cpu_steps, 2)
+            line['cpu_baseline'] = {'value': v, 'unit': 'cell-updates/s', 'cores': 1, 'kind': 'port',
+                                    'sample': '%d steps of the same workload on a %dx%d grid (%.1f s), '
+                                              'NumPy oracle, Python %d.%d; python2.7 %s' % (
+                                                  args.cpu_steps, args.cpu_size, args.cpu_size, el,
+                                                  sys.version_info[0], sys.version_info[1],
+                                                  'found' if _have_py27() else 'unavailable on this box')}
+    s.close()
+    D.close()
+    if line is not None:
+        print(json.dumps(line), flush=True)
+
+
+def _have_py27():
+    try:
+        return subprocess.run(['python2.7', '-c', 'import numpy'], capture_output=True, timeout=10).returncode == 0
+    except Exception:
+        return False
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    size = args.cpu_size
+    # one "step" = one update of the reference algorithm on the bounded sample
+    from oracle import channels as och  # noqa: F401  (the reference arm times the oracle port)
+    v, el = cpu_path(args.wave, size, args.steps, max(args.warmup, 0))
+    line = {
+        'impl': 'reference', 'metric': 'grid cell-updates/sec (fp64 routing step)', 'value': v,
+        'unit': 'cell-updates/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': el / args.steps * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+        'config': {'workload': 'synthetic fractal DEM, %s-wave channels, Manning, uniform rain pulse; '
+                               'CPU sample %dx%d of the %dx%d workload' % (args.wave, size, size, args.size, args.size),
+                   'wave': args.wave},
+        'cpu_baseline': {'value': v, 'unit': 'cell-updates/s', 'cores': 1, 'kind': 'port',
+                         'sample': '%d steps on a %dx%d grid; NumPy restatement of channels_base.update() '
+                                   '(the reference itself is Python 2.7 only; python2.7 %s)' % (
+                                       args.steps, size, size,
+                                       'found' if _have_py27() else 'unavailable on this box')},
+        'e2e': {'value': v, 'unit': 'cell-updates/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--size', type=int, default=16384, help='rows = columns per GPU')
+    ap.add_argument('--wave', default='kinematic', choices=sorted(WAVE_ID))
+    ap.add_argument('--generic', action='store_true', help='float64 parameter rasters (no packing)')
+    ap.add_argument('--cpu-size', type=int, default=1024)
+    ap.add_argument('--cpu-steps', type=int, default=20)
+    ap.add_argument('--no-cpu', action='store_true')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == '__main__':
+    main()

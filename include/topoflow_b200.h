@@ -1,0 +1,235 @@
+/* topoflow_b200.h -- C ABI of libtopoflow_b200.so
+ *
+ * B200 (sm_100a) implementation of TopoFlow 3.5's per-timestep D8 channel
+ * routing and of the D8 grid builder it runs on.  The reference
+ * (peckhams/topoflow_old) is pure Python/NumPy and has no FFI of its own; each
+ * entry point below names the reference method(s) it stands in for, as
+ * topoflow/<file>:<line>.  The Python shim in topoflow_old_b200/ binds these
+ * with ctypes; INTEGRATION.md shows the same binding written inside the
+ * reference's own components.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; the message
+ *     is available from tf_last_error() (thread-local to the calling thread);
+ *   - all pointers are HOST pointers to dense row-major [ny][nx] grids (row 0
+ *     = north) unless a parameter says otherwise; sizes are in elements;
+ *   - a handle owns every device buffer; nothing is shared between handles;
+ *   - one handle = one row strip of a (possibly larger) global grid on one
+ *     GPU.  With a single strip the strip is the grid.
+ */
+#ifndef TOPOFLOW_B200_H
+#define TOPOFLOW_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct tf_handle_s* tf_handle;
+
+/* ---- selectors ---------------------------------------------------------- */
+enum tf_wave { TF_KINEMATIC = 0, TF_DIFFUSIVE = 1, TF_DYNAMIC = 2 };
+enum tf_law  { TF_MANNING = 0, TF_LAW_OF_WALL = 1 };
+
+/* static channel parameters (channels_base.py:2142-2200, :797-984) */
+enum tf_param {
+    TF_P_WIDTH = 0,     /* bottom width [m], after "width == 0 -> dw"        */
+    TF_P_TAN_ANGLE = 1, /* tan(bank angle), host libm (np.tan)               */
+    TF_P_COS_ANGLE = 2, /* cos(bank angle), host libm (np.cos)               */
+    TF_P_SLOPE = 3,     /* S_bed = slope / sinu, after remove_bad_slopes     */
+    TF_P_ROUGH = 4,     /* nval (Manning) or z0val (law of the wall)         */
+    TF_P_DS = 5,        /* sinu * d8.ds, the channel flow length [m]         */
+    TF_P_COUNT = 6
+};
+
+/* grids that tf_chan_get / tf_chan_set_state understand */
+enum tf_field {
+    TF_F_VOL = 0, TF_F_D = 1, TF_F_U = 2, TF_F_Q = 3,   /* materialised state */
+    TF_F_QNEXT = 4,     /* u * A_wet of the last step = next step's Q         */
+    TF_F_F = 5, TF_F_RH = 6, TF_F_A_WET = 7, TF_F_P_WET = 8, TF_F_TAU = 9,
+    TF_F_U_STAR = 10, TF_F_FROUDE = 11, TF_F_S_FREE = 12,   /* derived on call */
+    TF_F_WIDTH = 13,    /* width with the overbank substitution applied       */
+    TF_F_MUTATED = 14,  /* 1.0 where "top_width > dw" has fired, else 0.0     */
+    TF_F_COUNT = 15
+};
+
+/* D8 products that tf_d8_get understands (element type in brackets) */
+enum tf_d8_field {
+    TF_D8_CODE = 0,       /* [uint8]   d8_grid                               */
+    TF_D8_PARENT_ID = 1,  /* [int32]   parent_ID_grid                        */
+    TF_D8_DS = 2,         /* [float32] flow length                           */
+    TF_D8_DW = 3,         /* [float32] flow width                            */
+    TF_D8_AREA = 4,       /* [float32] contributing area                     */
+    TF_D8_INMASK = 5,     /* [uint8]   bit k set: the k-th child direction   */
+    TF_D8_RAW = 6         /* [int16]   working codes before the uint8 cast   */
+};
+
+/* diversion point sets (channels_base.py:1226-1297) */
+enum tf_points { TF_PT_SOURCES = 0, TF_PT_SINKS = 1, TF_PT_CANALS_IN = 2,
+                 TF_PT_CANALS_OUT = 3 };
+
+/* ---- lifetime ------------------------------------------------------------ */
+
+/* Last error message of the calling thread ("" if none). */
+const char* tf_last_error(void);
+
+/* Library/build identification, e.g. "topoflow_b200 0.1 sm_100a". */
+const char* tf_version(void);
+
+/* Number of CUDA devices visible, or -1 on error (no compute is started). */
+int tf_device_count(void);
+
+/* Create a strip of ny rows x nx columns on CUDA device `device`.
+ * Replaces the array allocations spread over channels_component.initialize()
+ * (channels_base.py:467-571) and d8_component.initialize_computed_vars()
+ * (d8_base.py:505-519).  flags: reserved, pass 0. */
+int tf_create(int nx, int ny, int device, unsigned flags, tf_handle* out);
+
+/* Place the strip inside a larger grid of global_ny rows: its first row is
+ * global row `row_offset`; has_north / has_south say whether another strip
+ * (not the grid border) lies beyond its first / last row.  Call before
+ * tf_d8_build.  No counterpart in the reference (single process). */
+int tf_set_strip(tf_handle h, int row_offset, int global_ny, int has_north,
+                 int has_south);
+
+/* Free every device buffer of the handle (channels_base.py:708-722 finalize). */
+int tf_destroy(tf_handle h);
+
+/* Block until all work queued on the handle has finished. */
+int tf_sync(tf_handle h);
+
+/* ---- D8 grid builder ------------------------------------------------------ */
+
+/* Flow codes, parent IDs, ds, dw and the child mask from a DEM.
+ * Replaces d8_component.update_most(): update_flow_grid (d8_global.py:97-144:
+ * start_new_d8_codes :179-334, break_flow_grid_ties :352-367, link_flats
+ * :371-567), update_parent_ID_grid (:574-644), update_flow_width_grid
+ * (:863-935), update_flow_length_grid (:949-1004), update_noflow_IDs
+ * (:839-859).
+ *   dem        float32 [ny][nx]
+ *   dx,dy,dd   float32 [ny] per-row pixel sizes (d8_base.py:559-573)
+ *   nodata     cells <= nodata or non-finite get code 0 (d8_base.py:184)
+ *   link_flats / lr_periodic / tb_periodic : the cfg switches of the same name
+ *   stats_out  optional int64[4]: n_flats, n_pits, n_nodata, link_flats reps */
+int tf_d8_build(tf_handle h, const float* dem, const float* dx,
+                const float* dy, const float* dd, float nodata,
+                int link_flats, int lr_periodic, int tb_periodic,
+                int64_t* stats_out);
+
+/* Install a ready-made uint8 D8 code grid instead of deriving it from a DEM
+ * (what the pre-3.5 tf_d8_base did with <site>_flow.rtg; d8_global.py:162-166).
+ * Derives parent IDs, ds, dw and the child mask exactly as tf_d8_build. */
+int tf_d8_set_codes(tf_handle h, const uint8_t* codes, const float* dx,
+                    const float* dy, const float* dd,
+                    int lr_periodic, int tb_periodic);
+
+/* Contributing area.  Replaces d8_component.update_area_grid
+ * (d8_global.py:1018-1261).  da_rows: float64 [ny] cell area per row in m^2
+ * (pixels.py:174-200); units_km != 0 divides by 1e6 first (A_units 'km^2').
+ * n_unresolved_out (optional) counts flowing cells left at 0 (cycles). */
+int tf_d8_area(tf_handle h, const double* da_rows, int units_km,
+               int64_t* n_unresolved_out);
+
+/* Copy one D8 product to a dense host grid of the field's element type. */
+int tf_d8_get(tf_handle h, int which, void* host_out);
+
+/* ---- channel routing ------------------------------------------------------ */
+
+/* One static parameter, as a float64 grid (grid != NULL) or a scalar
+ * broadcast to every cell.  is_grid_in_reference tells whether the reference
+ * holds this variable as a grid: only grid-typed width / angle are rewritten
+ * by the overbank rule (channels_base.py:1449-1454). */
+int tf_chan_set_param(tf_handle h, int which, const double* grid,
+                      double scalar, int is_grid_in_reference);
+
+/* Fix the run configuration and build the device layout.  Call after
+ * tf_d8_build/tf_d8_set_codes and after all six tf_chan_set_param calls.
+ * Replaces set_computed_input_vars (channels_base.py:726-752) and the rest of
+ * initialize_computed_vars (:797-984).
+ *   wave        enum tf_wave  (cfg_extension, :732-736)
+ *   law         enum tf_law   (MANNING / LAW_OF_WALL cfg switches)
+ *   dt          channel time step [s]
+ *   da_rows     float64 [ny] cell area per row [m^2]
+ *   outlet_rc   int32 [2*n_outlets] (row, col) pairs; pair 0 is outlet_ID
+ *   allow_packed  != 0 lets the library store parameters that are exactly
+ *                 representable in float32 as float32 and bank angles as a
+ *                 table index; results are unchanged, traffic is lower. */
+int tf_chan_init(tf_handle h, int wave, int law, double dt,
+                 const double* da_rows, const int32_t* outlet_rc,
+                 int n_outlets, int allow_packed);
+
+/* Density of water [kg m-3] used for tau and u_star (the met component's
+ * 'water-liquid__mass-per-volume_density', channels_base.py:165, :1577). */
+int tf_chan_set_rho(tf_handle h, double rho);
+
+/* Overwrite one materialised state grid (TF_F_VOL, TF_F_D, TF_F_U, TF_F_QNEXT)
+ * with host data: the initial state of initialize_computed_vars
+ * (channels_base.py:900-960), or a restart. */
+int tf_chan_set_state(tf_handle h, int which, const double* grid);
+
+/* Excess rain rate R = (P_rain + SM + GW + MR) - (ET + IN) [m/s]
+ * (channels_base.py:1103-1147), as a grid or a scalar.  sum_out (optional)
+ * receives sum over the strip of (R*da)*dt, the per-step increment of vol_R
+ * (update_R_integral, :1151-1160). */
+int tf_chan_set_R(tf_handle h, const double* grid, double scalar,
+                  double* sum_out);
+
+/* Diversion point data (channels_base.py:1226-1297).  rows/cols int32[n];
+ * values float64[n]: sources_Q, sinks_Q, canals_Q_fraction or canals_out_Q. */
+int tf_chan_set_points(tf_handle h, int kind, const int32_t* rows,
+                       const int32_t* cols, const double* values, int n);
+
+/* Advance n_steps time steps: update_discharge .. check_flow_velocity of
+ * channels_component.update() (channels_base.py:602-672) per step.
+ *   taps_out      float64 [n_steps][n_outlets][4] = Q, u, d, f at the outlets
+ *                 after each step (update_outlet_values, :1812-1832)
+ *   canals_in_out float64 [n_steps][n_canals] canals_in_Q (:1283), or NULL
+ *   bad_out       int64[2]: first cell (row-major index) with a negative or
+ *                 non-finite depth, then velocity, -1 if none
+ *                 (check_flow_depth :1982-2030, check_flow_velocity :2034-2080)
+ * Host buffers; the copies are part of the call. */
+int tf_chan_step(tf_handle h, int n_steps, double* taps_out,
+                 double* canals_in_out, int64_t* bad_out);
+
+/* Same work, nothing copied back: queue n_steps on the handle's stream and
+ * return.  Used to time the kernels with inputs resident in HBM. */
+int tf_chan_step_async(tf_handle h, int n_steps);
+
+/* Copy one grid (enum tf_field) to a dense float64 host grid.  Derived fields
+ * are recomputed from the state the way update_trapezoid_Rh (:1590-1643),
+ * update_shear_stress/speed (:1567-1586), update_friction_factor (:1654-1721)
+ * and update_froude_number (:1795-1808) do. */
+int tf_chan_get(tf_handle h, int which, double* host_out);
+
+/* Interior min/max of Q, u, d: out[6] = Qmin,Qmax,umin,umax,dmin,dmax
+ * (update_mins_and_maxes, channels_base.py:1890-1916). */
+int tf_chan_minmax(tf_handle h, double* out6);
+
+/* Device-side timing of everything queued by tf_chan_step* since the last
+ * call: out[0] = elapsed ms (CUDA events on the handle's stream), out[1] =
+ * steps, out[2] = kernel launches, out[3] = bytes per cell-update actually
+ * addressed by the step kernels for the current layout. */
+int tf_chan_timing(tf_handle h, double* out4);
+
+/* ---- row-strip decomposition over several GPUs ---------------------------- */
+
+/* 128-byte NCCL unique id for tf_comm_init (rank 0 creates, all ranks use). */
+int tf_comm_unique_id(uint8_t* id128);
+
+/* Join a communicator of `nranks` strips stacked north to south; rank r's
+ * north neighbour is r-1.  After this, tf_chan_step* exchanges one halo row
+ * of Q (plus d and u for the diffusive / dynamic wave) with each neighbour
+ * per step over NCCL send/recv.  The reference has no counterpart: it is
+ * single-process (docs/Peckham_2014_EMELI_FINAL.pdf). */
+int tf_comm_init(tf_handle h, int rank, int nranks, const uint8_t* id128);
+
+/* Set the halo DEM rows by hand (single process tests): north/south float32
+ * [nx] or NULL for "no neighbour" (global border). */
+int tf_d8_set_halo_dem(tf_handle h, const float* north_row,
+                       const float* south_row);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TOPOFLOW_B200_H */

@@ -1,0 +1,47 @@
+// tf_chan_host.cuh -- host helpers shared by the routing translation units.
+#pragma once
+#include "tf_chan_kernels2.cuh"
+#include "tf_common.cuh"
+
+// ---------------------------------------------------------------------------
+static inline ChanArgs chan_args(tf_handle h, int y_begin, int y_end) {
+    ChanArgs a;
+    memset(&a, 0, sizeof(a));
+    const Geom& g = h->g;
+    a.nx = g.nx; a.ny = g.ny; a.pitch = g.pitch;
+    a.y_begin = y_begin; a.y_end = y_end;
+    a.row_offset = g.row_offset; a.global_ny = g.global_ny;
+    a.dt = h->dt; a.rho = h->rho;
+    a.Q = h->Qcur; a.Qn = h->Qnext;
+    a.vol = h->vol.p; a.d = h->d.p; a.u = h->u.p; a.u_old = h->u2.p;
+    a.sfree = h->sfree.p;
+    a.Rgrid = h->R_is_grid ? h->R.p : nullptr;
+    a.Rs = h->R_scalar;
+    a.da_rows = h->da_rows + 1;
+    a.code = h->code.p; a.inmask = h->inmask.p; a.dw = h->dw.p;
+    a.mstate = h->mstate.p;
+    a.mut_width = h->mut_width; a.mut_angle = h->mut_angle;
+    a.w64 = h->w64.p; a.tan64 = h->tan64.p; a.cos64 = h->cos64.p;
+    a.S64 = h->S64.p; a.n64 = h->n64.p; a.ds64 = h->ds64.p;
+    a.w32 = h->w32.p; a.S32 = h->S32.p; a.n32 = h->n32.p; a.ds32 = h->ds32.p;
+    a.aidx = h->aidx.p; a.lut = h->lut;
+    a.bad = h->bad;
+    return a;
+}
+
+static inline dim3 tile_grid(const Geom& g, int rows) {
+    return dim3((g.pitch / 4 + 31) / 32, (rows + 7) / 8);
+}
+
+// PACKED x LAW dispatch
+#define TF_DISPATCH(h, EXPR)                                              \
+    do {                                                                  \
+        if ((h)->packed) {                                                \
+            if ((h)->law == 0) { constexpr bool P = true; constexpr int L = 0; EXPR; }  \
+            else { constexpr bool P = true; constexpr int L = 1; EXPR; }  \
+        } else {                                                          \
+            if ((h)->law == 0) { constexpr bool P = false; constexpr int L = 0; EXPR; } \
+            else { constexpr bool P = false; constexpr int L = 1; EXPR; } \
+        }                                                                 \
+    } while (0)
+

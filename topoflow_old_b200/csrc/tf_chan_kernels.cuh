@@ -1,0 +1,234 @@
+// tf_chan_kernels.cuh -- the routing kernels.
+//
+// Thread layout: a warp owns 128 consecutive cells of one row, 4 per lane, so
+// every raster access is a 128-bit (float64 / float32) or 32-bit (uint8) load
+// per lane and fully coalesced per warp.  A block is 32 x 8 threads = a tile
+// of 128 columns x 8 rows; vertical neighbours are mostly served by the
+// block's own L1 lines, the rest by L2.
+//
+// The eight-neighbour inflow uses the per-cell child mask built with the D8
+// grid (tf_d8.cu:k_inmask): bit j set means "the neighbour opposite to
+// direction j drains into me", and bits are visited in ascending j, which is
+// the reference's k = 1..8 order (channels_base.py:1346-1361).  The running
+// sum stays in registers.
+#pragma once
+#include "tf_chan_math.cuh"
+
+struct ChanArgs {
+    int nx, ny, pitch;
+    int y_begin, y_end;            // rows this launch covers
+    int row_offset, global_ny;     // strip placement (bad-cell index, borders)
+    double dt, rho;
+    // state
+    const double* Q;               // Q of this step (read with halo)
+    double* Qn;                    // u * A_wet, next step's Q
+    double* vol;
+    double* d;
+    double* u;                     // velocity written by this step
+    const double* u_old;           // dynamic wave: last step's velocity
+    double* sfree;                 // diffusive / dynamic
+    const double* Rgrid;           // NULL -> Rs
+    double Rs;
+    const double* da_rows;         // [y], y = -1 .. ny
+    // D8
+    const uint8_t* code;
+    const uint8_t* inmask;
+    const float* dw;
+    uint8_t* mstate;               // bit0: overbank rule has fired; bit1: fires next step
+    int mut_width, mut_angle;
+    // parameters, generic layout
+    const double *w64, *tan64, *cos64, *S64, *n64, *ds64;
+    // parameters, packed layout
+    const float *w32, *S32, *n32, *ds32;
+    const uint8_t* aidx;
+    const double* lut;             // [256] tan, [256] cos
+    long long* bad;                // [0] depth, [1] velocity: min bad global index
+};
+
+// ---------------------------------------------------------------------------
+template <bool PACKED>
+__device__ __forceinline__ void load_shape(const ChanArgs& a, int64_t i, double (&w)[4],
+                                           double (&t)[4], double (&c)[4], double (&ds)[4]) {
+    if (PACKED) {
+        ld4(a.w32 + i, w);
+        ld4(a.ds32 + i, ds);
+        int ai[4];
+        ld4(a.aidx + i, ai);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            t[k] = __ldg(a.lut + ai[k]);
+            c[k] = __ldg(a.lut + 256 + ai[k]);
+        }
+    } else {
+        ld4(a.w64 + i, w);
+        ld4(a.ds64 + i, ds);
+        ld4(a.tan64 + i, t);
+        ld4(a.cos64 + i, c);
+    }
+}
+
+template <bool PACKED>
+__device__ __forceinline__ void load_slope_rough(const ChanArgs& a, int64_t i, double (&S)[4],
+                                                 double (&n)[4]) {
+    if (PACKED) {
+        ld4(a.S32 + i, S);
+        ld4(a.n32 + i, n);
+    } else {
+        ld4(a.S64 + i, S);
+        ld4(a.n64 + i, n);
+    }
+}
+
+// overbank rule, channels_base.py:1449-1454: once "top_width > dw" has fired
+// the cell is a rectangle as wide as the flow width
+__device__ __forceinline__ void apply_overbank(const ChanArgs& a, int m, double dw, double& w,
+                                               double& t, double& c) {
+    if (m) {
+        if (a.mut_width) w = dw;
+        if (a.mut_angle) { t = 0.0; c = 1.0; }
+    }
+}
+
+// offset of the child that bit j of the mask stands for
+__device__ __forceinline__ int64_t child_offset(int j, int pitch) {
+    // neighbour j is at (dr, dc); the child sits opposite: (-dr, -dc)
+    const int dr = (j == 0 || j >= 6) ? -1 : ((j >= 2 && j <= 4) ? 1 : 0);
+    const int dc = (j <= 2) ? 1 : ((j >= 4 && j <= 6) ? -1 : 0);
+    return -((int64_t)dr * pitch + dc);
+}
+
+__device__ __forceinline__ void flag_bad(const ChanArgs& a, int which, int x, int y) {
+    const long long gid = (long long)(y + a.row_offset) * a.nx + x;
+    atomicMin(reinterpret_cast<long long*>(a.bad + which), gid);
+}
+
+// ---------------------------------------------------------------------------
+// mass balance + trapezoid depth for 4 cells (update_flow_volume :1308-1375,
+// update_flow_depth :1379-1532).  Returns the effective shape in w, t, c.
+// ---------------------------------------------------------------------------
+template <bool PACKED>
+__device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int y, int64_t i,
+                                                 double (&Q)[4], double (&v)[4], double (&d)[4],
+                                                 double (&w)[4], double (&t)[4], double (&c)[4],
+                                                 double (&ds)[4], double (&dwv)[4], int (&code)[4],
+                                                 int (&m)[4]) {
+    int mask[4], ms[4];
+    ld4(a.Q + i, Q);
+    ld4c(a.vol + i, v);
+    ld4(a.code + i, code);
+    ld4(a.inmask + i, mask);
+    {
+        const uchar4 s = *reinterpret_cast<const uchar4*>(a.mstate + i);
+        ms[0] = s.x; ms[1] = s.y; ms[2] = s.z; ms[3] = s.w;
+    }
+    load_shape<PACKED>(a, i, w, t, c, ds);
+    ld4(a.dw + i, dwv);
+    double R[4];
+    if (a.Rgrid) ld4(a.Rgrid + i, R);
+    else { R[0] = R[1] = R[2] = R[3] = a.Rs; }
+    const double da = a.da_rows[y];
+    const double dt = a.dt;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        m[k] = (ms[k] & 1) | ((ms[k] >> 1) & 1);
+        apply_overbank(a, m[k], dwv[k], w[k], t[k], c[k]);
+        double acc = v[k] + (R[k] * da) * dt;                  // :1334
+        int mk = mask[k];
+        while (mk) {                                           // :1346-1361
+            const int j = __ffs(mk) - 1;
+            mk &= mk - 1;
+            acc += dt * __ldg(a.Q + i + k + child_offset(j, a.pitch));
+        }
+        acc -= Q[k] * dt;                                      // :1366
+        acc = np_max0(acc);                                    // :1375
+        v[k] = acc;
+        double dd = chan_depth(acc, w[k], t[k], ds[k]);
+        if (code[k] == 0) dd = 0.0;                            // :1511
+        d[k] = np_max0(dd);                                    // :1526
+    }
+    (void)x4;
+}
+
+// next step's overbank test with this step's depth (:1449-1450), packed into
+// the state byte; written only when it changes
+__device__ __forceinline__ void store_mstate(const ChanArgs& a, int64_t i, const int (&m)[4],
+                                             const double (&d)[4], const double (&w)[4],
+                                             const double (&t)[4], const double (&dwv)[4]) {
+    const uchar4 old = *reinterpret_cast<const uchar4*>(a.mstate + i);
+    unsigned char nw[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const double top = w[k] + ((2.0 * d[k]) * t[k]);
+        nw[k] = (unsigned char)(m[k] | ((top > dwv[k]) ? 2 : 0));
+    }
+    if (nw[0] != old.x || nw[1] != old.y || nw[2] != old.z || nw[3] != old.w)
+        *reinterpret_cast<uchar4*>(a.mstate + i) = make_uchar4(nw[0], nw[1], nw[2], nw[3]);
+}
+
+// ---------------------------------------------------------------------------
+// kinematic wave: the whole step in one pass
+// ---------------------------------------------------------------------------
+template <bool PACKED, int LAW>
+__global__ void __launch_bounds__(256)
+k_step_kinematic(const ChanArgs a) {
+    const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
+    if (x4 >= a.pitch || y >= a.y_end) return;
+    const int64_t i = (int64_t)y * a.pitch + x4;
+    double Q[4], v[4], d[4], w[4], t[4], c[4], ds[4], dwv[4], S[4], n[4], u[4], Qn[4];
+    int code[4], m[4];
+    volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m);
+    load_slope_rough<PACKED>(a, i, S, n);
+    bool bad_d = false, bad_u = false;
+    int bx = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const bool noflow = (code[k] == 0);
+        const XSection xs = chan_xsection(d[k], w[k], t[k], c[k], noflow);
+        double uu = chan_velocity<LAW>(xs.Rh, S[k], n[k], d[k]);   // kinematic: S = S_bed
+        if (noflow) uu = 0.0;                                      // :1783-1791
+        u[k] = uu;
+        Qn[k] = uu * xs.A_wet;                                     // :1188 of the next step
+        if (x4 + k < a.nx) {
+            if (bad_value(d[k]) && !bad_d) { bad_d = true; bx = x4 + k; }
+            if (bad_value(uu) && !bad_u) { bad_u = true; if (!bad_d) bx = x4 + k; }
+        }
+    }
+    st4(a.vol + i, v);
+    st4(a.d + i, d);
+    st4(a.u + i, u);
+    st4(a.Qn + i, Qn);
+    store_mstate(a, i, m, d, w, t, dwv);
+    if (bad_d || bad_u) {
+        // report the first offending cell of each kind in this segment
+#pragma unroll
+        for (int k = 3; k >= 0; --k) {
+            if (x4 + k < a.nx) {
+                if (bad_value(d[k])) flag_bad(a, 0, x4 + k, y);
+                if (bad_value(u[k])) flag_bad(a, 1, x4 + k, y);
+            }
+        }
+    }
+    (void)bx;
+}
+
+// ---------------------------------------------------------------------------
+// diffusive / dynamic wave, phase A: volume and depth of every cell
+// ---------------------------------------------------------------------------
+template <bool PACKED>
+__global__ void __launch_bounds__(256)
+k_phase_a(const ChanArgs a) {
+    const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
+    if (x4 >= a.pitch || y >= a.y_end) return;
+    const int64_t i = (int64_t)y * a.pitch + x4;
+    double Q[4], v[4], d[4], w[4], t[4], c[4], ds[4], dwv[4];
+    int code[4], m[4];
+    volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m);
+    st4(a.vol + i, v);
+    st4(a.d + i, d);
+    store_mstate(a, i, m, d, w, t, dwv);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (x4 + k < a.nx && bad_value(d[k])) flag_bad(a, 0, x4 + k, y);
+}

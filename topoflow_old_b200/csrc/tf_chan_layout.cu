@@ -1,0 +1,129 @@
+// tf_chan_layout.cu -- turn the host parameter grids into the device layout.
+//
+// Two layouts exist, chosen once in tf_chan_init:
+//   generic : width, tan, cos, S_bed, roughness, ds as float64 rasters;
+//   packed  : width, S_bed, roughness, ds as float32 rasters and the bank
+//             angle as a one-byte index into a (tan, cos) table.
+// The packed layout is used only when it is EXACT: every value must survive
+// the float64 -> float32 -> float64 round trip (true for anything the
+// reference read from an RTG file, which is float32 on disk,
+// channels_base.py:2150-2153) and the grid must hold at most 255 distinct
+// bank angles.  Arithmetic is float64 in both layouts; only the bytes read
+// per cell differ.
+#include <map>
+#include <utility>
+
+#include "tf_chan_host.cuh"
+
+static bool f32_exact(const HostParam& p) {
+    if (p.grid.empty()) {
+        const double v = p.scalar;
+        return (double)(float)v == v;
+    }
+    for (double v : p.grid)
+        if (!((double)(float)v == v)) return false;
+    return true;
+}
+
+static inline double hp_at(const HostParam& p, size_t i) {
+    return p.grid.empty() ? p.scalar : p.grid[i];
+}
+
+template <typename T>
+static int fill_raster(tf_handle h, Raster<T>& r, const HostParam& p, T pad) {
+    const Geom& g = h->g;
+    TF_TRY(raster_alloc(h, r, 0));
+    std::vector<T> host((size_t)g.n_alloc, pad);
+    for (int y = 0; y < g.ny; ++y) {
+        T* row = host.data() + g.origin + (size_t)y * g.pitch;
+        for (int x = 0; x < g.nx; ++x) row[x] = (T)hp_at(p, (size_t)y * g.nx + x);
+    }
+    TF_CUDA(cudaMemcpy(r.base, host.data(), sizeof(T) * (size_t)g.n_alloc, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int chan_layout_init(tf_handle h, int allow_packed) {
+    const Geom& g = h->g;
+    const size_t n = (size_t)g.nx * g.ny;
+    const HostParam& W = h->hp[TF_P_WIDTH];
+    const HostParam& T = h->hp[TF_P_TAN_ANGLE];
+    const HostParam& C = h->hp[TF_P_COS_ANGLE];
+    const HostParam& S = h->hp[TF_P_SLOPE];
+    const HostParam& N = h->hp[TF_P_ROUGH];
+    const HostParam& D = h->hp[TF_P_DS];
+    TF_CHECK(T.grid.empty() == C.grid.empty(),
+             "tf_chan_init: tan and cos of the bank angle must both be grids or both scalars");
+
+    bool packed = allow_packed && f32_exact(W) && f32_exact(S) && f32_exact(N) && f32_exact(D);
+    std::vector<uint8_t> aidx;
+    std::vector<double> lut(512, 0.0);
+    if (packed) {
+        // entry 0 is the rectangle (tan 0, cos 1) the overbank rule switches to
+        std::map<std::pair<uint64_t, uint64_t>, int> seen;
+        auto bits = [](double v) { uint64_t b; memcpy(&b, &v, 8); return b; };
+        lut[0] = 0.0; lut[256] = 1.0;
+        seen[{bits(0.0), bits(1.0)}] = 0;
+        int n_used = 1;
+        const size_t n_ang = T.grid.empty() ? 1 : n;
+        aidx.assign(n, 0);
+        uint64_t last_t = ~0ull, last_c = ~0ull;
+        int last_i = -1;
+        for (size_t i = 0; i < n_ang && packed; ++i) {
+            const uint64_t bt = bits(hp_at(T, i)), bc = bits(hp_at(C, i));
+            int idx;
+            if (bt == last_t && bc == last_c) idx = last_i;
+            else {
+                auto it = seen.find({bt, bc});
+                if (it != seen.end()) idx = it->second;
+                else if (n_used < 256) {
+                    idx = n_used++;
+                    seen[{bt, bc}] = idx;
+                    lut[idx] = hp_at(T, i);
+                    lut[256 + idx] = hp_at(C, i);
+                } else { packed = false; break; }
+                last_t = bt; last_c = bc; last_i = idx;
+            }
+            aidx[i] = (uint8_t)idx;
+        }
+        if (packed && T.grid.empty()) std::fill(aidx.begin(), aidx.end(), aidx[0]);
+    }
+    h->packed = packed ? 1 : 0;
+
+    // padding cells get a harmless shape (unit rectangle, code 0 keeps them dry)
+    if (packed) {
+        TF_TRY(fill_raster<float>(h, h->w32, W, 1.0f));
+        TF_TRY(fill_raster<float>(h, h->S32, S, 1.0f));
+        TF_TRY(fill_raster<float>(h, h->n32, N, 1.0f));
+        TF_TRY(fill_raster<float>(h, h->ds32, D, 1.0f));
+        HostParam A;
+        A.grid.assign(aidx.begin(), aidx.end());
+        TF_TRY(fill_raster<uint8_t>(h, h->aidx, A, (uint8_t)0));
+        if (!h->lut) TF_CUDA(cudaMalloc((void**)&h->lut, sizeof(double) * 512));
+        TF_CUDA(cudaMemcpy(h->lut, lut.data(), sizeof(double) * 512, cudaMemcpyHostToDevice));
+    } else {
+        TF_TRY(fill_raster<double>(h, h->w64, W, 1.0));
+        TF_TRY(fill_raster<double>(h, h->S64, S, 1.0));
+        TF_TRY(fill_raster<double>(h, h->n64, N, 1.0));
+        TF_TRY(fill_raster<double>(h, h->ds64, D, 1.0));
+        TF_TRY(fill_raster<double>(h, h->tan64, T, 0.0));
+        TF_TRY(fill_raster<double>(h, h->cos64, C, 1.0));
+    }
+    // the flow width of padding cells must never trip the overbank test
+    {
+        std::vector<float> dw((size_t)g.n_alloc);
+        TF_CUDA(cudaMemcpy(dw.data(), h->dw.base, sizeof(float) * (size_t)g.n_alloc, cudaMemcpyDeviceToHost));
+        for (int y = -1; y <= g.ny; ++y) {
+            float* row = dw.data() + g.origin + (int64_t)y * g.pitch;
+            for (int x = 0; x < g.pitch; ++x)
+                if (y < 0 || y >= g.ny || x >= g.nx) row[x] = 3.0e38f;
+        }
+        TF_CUDA(cudaMemcpy(h->dw.base, dw.data(), sizeof(float) * (size_t)g.n_alloc, cudaMemcpyHostToDevice));
+    }
+    // free the host copies: the device rasters are the parameters from here on
+    for (int k = 0; k < TF_P_COUNT; ++k) {
+        h->hp[k].grid.clear();
+        h->hp[k].grid.shrink_to_fit();
+        h->hp[k].set = false;
+    }
+    return 0;
+}

@@ -1,0 +1,111 @@
+// tf_chan_math.cuh -- per-cell arithmetic of the channel step.
+//
+// Every expression keeps the association NumPy used in the reference
+// (left to right, no fused multiply-add: this TU is built with -fmad=false),
+// so vol and d are reproduced bit for bit from bit-identical inputs.  The
+// only operations that are not correctly rounded are the cube root (the
+// reference's x**(1/3), x**(2/3)) and log, both within ~2 ulp.
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "../../include/topoflow_b200.h"
+
+#define TF_G 9.81                    // channels_base.py:456
+#define TF_AVAL 0.476                // :457
+#define TF_KAPPA 0.408               // :458
+
+// np.maximum(x, 0): NaN propagates (fmax would swallow it)
+__device__ __forceinline__ double np_max0(double x) {
+    return (x != x) ? x : (x > 0.0 ? x : 0.0);
+}
+__device__ __forceinline__ double np_maxv(double x, double lo) {
+    return (x != x) ? x : (x > lo ? x : lo);
+}
+
+// update_flow_depth, channels_base.py:1465-1486
+__device__ __forceinline__ double chan_depth(double vol, double w, double t, double ds) {
+    if (t == 0.0) {
+        return vol / (w * ds);
+    }
+    const double denom = 2.0 * t;
+    double arg = ((2.0 * denom) * vol) / ds;
+    arg += w * w;
+    return (sqrt(arg) - w) / denom;
+}
+
+// update_trapezoid_Rh, channels_base.py:1615-1643
+struct XSection { double A_wet, P_wet, Rh; };
+__device__ __forceinline__ XSection chan_xsection(double d, double w, double t, double c, bool noflow) {
+    XSection s;
+    const double L2 = d * t;
+    s.A_wet = d * (w + L2);
+    s.P_wet = w + ((2.0 * d) / c);
+    if (noflow) s.P_wet = 1.0;
+    s.Rh = s.A_wet / s.P_wet;
+    if (noflow) s.Rh = 0.0;
+    return s;
+}
+
+// x ** (2/3) for x >= 0 (NaN and inf pass through like pow)
+__device__ __forceinline__ double pow_two_thirds(double x) {
+    const double c = cbrt(x);
+    return c * c;
+}
+
+// manning_formula :2561-2589 / law_of_the_wall :2593-2640
+template <int LAW>
+__device__ __forceinline__ double chan_velocity(double Rh, double S, double rough, double d) {
+    if (LAW == 0) {
+        return (pow_two_thirds(Rh) * sqrt(S)) / rough;
+    } else {
+        double sm = (TF_AVAL / rough) * d;
+        sm = np_maxv(sm, 1.1);
+        const double law_const = sqrt(TF_G) / TF_KAPPA;     // :459
+        return (law_const * sqrt(Rh * S)) * log(sm);
+    }
+}
+
+// update_friction_factor :1654-1721
+template <int LAW>
+__device__ __forceinline__ double chan_friction(double d, double rough) {
+    if (!(d > 0.0)) return 0.0;
+    if (LAW == 0) {
+        return TF_G * ((rough * rough) / cbrt(d));
+    } else {
+        double sm = (TF_AVAL / rough) * d;
+        sm = np_maxv(sm, 1.1);
+        const double r = TF_KAPPA / log(sm);
+        return r * r;
+    }
+}
+
+__device__ __forceinline__ bool bad_value(double v) {
+    return (v < 0.0) || !isfinite(v);                        // :1992, :2044
+}
+
+// ---- 4-wide row segment loads / stores --------------------------------------
+__device__ __forceinline__ void ld4(const double* __restrict__ p, double (&o)[4]) {
+    const double2 a = __ldg(reinterpret_cast<const double2*>(p));
+    const double2 b = __ldg(reinterpret_cast<const double2*>(p) + 1);
+    o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+}
+__device__ __forceinline__ void ld4(const float* __restrict__ p, double (&o)[4]) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p));
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w;
+}
+__device__ __forceinline__ void ld4(const uint8_t* __restrict__ p, int (&o)[4]) {
+    const uchar4 a = __ldg(reinterpret_cast<const uchar4*>(p));
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w;
+}
+// plain (coherent) loads for buffers another kernel of the same step wrote
+__device__ __forceinline__ void ld4c(const double* p, double (&o)[4]) {
+    const double2 a = *reinterpret_cast<const double2*>(p);
+    const double2 b = *(reinterpret_cast<const double2*>(p) + 1);
+    o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+}
+__device__ __forceinline__ void st4(double* p, const double (&v)[4]) {
+    reinterpret_cast<double2*>(p)[0] = make_double2(v[0], v[1]);
+    reinterpret_cast<double2*>(p)[1] = make_double2(v[2], v[3]);
+}

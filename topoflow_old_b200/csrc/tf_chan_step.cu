@@ -1,0 +1,278 @@
+// tf_chan_step.cu -- the per-step launch sequence and the read-back entry
+// points of the routing path.
+#include "tf_chan_host.cuh"
+
+// one launch covering rows [y0, y1)
+static int launch_kinematic(tf_handle h, cudaStream_t s, int y0, int y1) {
+    ChanArgs a = chan_args(h, y0, y1);
+    TF_DISPATCH(h, (k_step_kinematic<P, L><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a)));
+    TF_CUDA(cudaGetLastError());
+    h->acc_launches++;
+    return 0;
+}
+
+static int launch_phase_a(tf_handle h, cudaStream_t s, int y0, int y1) {
+    ChanArgs a = chan_args(h, y0, y1);
+    if (h->packed) k_phase_a<true><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a);
+    else k_phase_a<false><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a);
+    TF_CUDA(cudaGetLastError());
+    h->acc_launches++;
+    return 0;
+}
+
+static int launch_phase_b(tf_handle h, cudaStream_t s, int y0, int y1) {
+    ChanArgs a = chan_args(h, y0, y1);
+    if (h->wave == TF_DIFFUSIVE)
+        TF_DISPATCH(h, (k_phase_b<P, L, 1><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a)));
+    else
+        TF_DISPATCH(h, (k_phase_b<P, L, 2><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a)));
+    TF_CUDA(cudaGetLastError());
+    h->acc_launches++;
+    return 0;
+}
+
+static int ensure_taps(tf_handle h, int n_steps) {
+    const int nc = h->pts[TF_PT_CANALS_IN].n;
+    if (n_steps <= h->taps_cap && h->taps && (nc == 0 || h->canal_taps)) return 0;
+    if (h->taps) cudaFree(h->taps);
+    if (h->canal_taps) cudaFree(h->canal_taps);
+    h->taps = nullptr; h->canal_taps = nullptr;
+    h->taps_cap = n_steps > 64 ? n_steps : 64;
+    const size_t n = (size_t)h->taps_cap * (h->n_outlets > 0 ? h->n_outlets : 1) * 4;
+    TF_CUDA(cudaMalloc((void**)&h->taps, sizeof(double) * n));
+    if (nc) TF_CUDA(cudaMalloc((void**)&h->canal_taps, sizeof(double) * (size_t)h->taps_cap * nc));
+    return 0;
+}
+
+// Queue n_steps on the handle's streams.  record != 0 stores the outlet taps
+// of step s in slot s of the device tap buffer.
+static int queue_steps(tf_handle h, int n_steps, int record) {
+    const Geom& g = h->g;
+    TF_CHECK(h->chan_ready, "tf_chan_step: call tf_chan_init first");
+    TF_CHECK(n_steps >= 0, "tf_chan_step: n_steps < 0");
+    if (record) TF_TRY(ensure_taps(h, n_steps));
+    cudaStream_t s = h->stream;
+    if (h->state_dirty) {
+        ChanArgs a = chan_args(h, 0, g.ny);
+        if (h->packed) k_init_mstate<true><<<tile_grid(g, g.ny), dim3(32, 8), 0, s>>>(a);
+        else k_init_mstate<false><<<tile_grid(g, g.ny), dim3(32, 8), 0, s>>>(a);
+        TF_CUDA(cudaGetLastError());
+        h->state_dirty = false;
+    }
+    if (!h->timing_open) {
+        TF_CUDA(cudaEventRecord(h->t0, s));
+        h->timing_open = true;
+    }
+    const bool any_points = h->pts[0].n || h->pts[1].n || h->pts[2].n || h->pts[3].n;
+    const bool multi = h->nccl_comm != nullptr;
+    for (int step = 0; step < n_steps; ++step) {
+        // the grid written as "next Q" by the previous step is this step's Q
+        double* t = h->Qcur; h->Qcur = h->Qnext; h->Qnext = t;
+        if (h->wave == TF_DYNAMIC) {   // last step's u becomes u_old
+            Raster<double> r = h->u; h->u = h->u2; h->u2 = r;
+        }
+        if (any_points) {
+            PointsArgs p;
+            for (int k = 0; k < 4; ++k) { p.n[k] = h->pts[k].n; p.idx[k] = h->pts[k].idx; p.val[k] = h->pts[k].val; }
+            p.tmp = h->pts_tmp;
+            p.canals_in_out = (record && h->canal_taps) ? h->canal_taps + (size_t)step * h->pts[TF_PT_CANALS_IN].n : nullptr;
+            k_diversions<<<1, 32, 0, s>>>(p, h->Qcur, h->vol.p, h->dt);
+            TF_CUDA(cudaGetLastError());
+            h->acc_launches++;
+            if (multi) {   // a diverted cell on an edge row changes the neighbour's halo
+                void* arr[1] = {h->Qcur};
+                size_t es[1] = {sizeof(double)};
+                TF_TRY(comm_exchange_rows(h, s, arr, es, 1));
+            }
+        }
+        if (h->wave == TF_KINEMATIC) {
+            if (!multi || g.ny < 32) {
+                TF_TRY(launch_kinematic(h, s, 0, g.ny));
+                if (multi) {
+                    void* arr[1] = {h->Qnext};
+                    size_t es[1] = {sizeof(double)};
+                    TF_TRY(comm_exchange_rows(h, s, arr, es, 1));
+                }
+            } else {
+                // edge bands first on the high-priority stream, their halo
+                // rows travel while the interior is computed
+                cudaStream_t e = h->stream_edge;
+                TF_CUDA(cudaEventRecord(h->ev_main, s));
+                TF_CUDA(cudaStreamWaitEvent(e, h->ev_main, 0));
+                TF_TRY(launch_kinematic(h, e, 0, 8));
+                TF_TRY(launch_kinematic(h, e, g.ny - 8, g.ny));
+                void* arr[1] = {h->Qnext};
+                size_t es[1] = {sizeof(double)};
+                TF_TRY(comm_exchange_rows(h, e, arr, es, 1));
+                TF_CUDA(cudaEventRecord(h->ev_edge, e));
+                TF_TRY(launch_kinematic(h, s, 8, g.ny - 8));
+                TF_CUDA(cudaStreamWaitEvent(s, h->ev_edge, 0));
+            }
+        } else {
+            TF_TRY(launch_phase_a(h, s, 0, g.ny));
+            if (multi) {
+                void* arr[1] = {h->d.p};
+                size_t es[1] = {sizeof(double)};
+                TF_TRY(comm_exchange_rows(h, s, arr, es, 1));
+            }
+            TF_TRY(launch_phase_b(h, s, 0, g.ny));
+            if (multi) {
+                void* arr[2] = {h->Qnext, h->u.p};
+                size_t es[2] = {sizeof(double), sizeof(double)};
+                TF_TRY(comm_exchange_rows(h, s, arr, es, h->wave == TF_DYNAMIC ? 2 : 1));
+            }
+        }
+        if (record && h->n_outlets) {
+            ChanArgs a = chan_args(h, 0, g.ny);
+            double* out = h->taps + (size_t)step * h->n_outlets * 4;
+            TF_DISPATCH(h, (k_taps<P, L><<<(h->n_outlets + 63) / 64, 64, 0, s>>>(a, h->outlet_idx, h->n_outlets, out)));
+            TF_CUDA(cudaGetLastError());
+            h->acc_launches++;
+        }
+    }
+    h->acc_steps += n_steps;
+    return 0;
+}
+
+extern "C" int tf_chan_step_async(tf_handle h, int n_steps) {
+    TF_TRY(use_device(h));
+    return queue_steps(h, n_steps, 0);
+}
+
+extern "C" int tf_chan_step(tf_handle h, int n_steps, double* taps_out, double* canals_in_out,
+                            int64_t* bad_out) {
+    TF_TRY(use_device(h));
+    TF_TRY(queue_steps(h, n_steps, taps_out != nullptr || canals_in_out != nullptr));
+    cudaStream_t s = h->stream;
+    if (taps_out && h->n_outlets && n_steps)
+        TF_CUDA(cudaMemcpyAsync(taps_out, h->taps, sizeof(double) * (size_t)n_steps * h->n_outlets * 4,
+                                cudaMemcpyDeviceToHost, s));
+    const int nc = h->pts[TF_PT_CANALS_IN].n;
+    if (canals_in_out && nc && n_steps)
+        TF_CUDA(cudaMemcpyAsync(canals_in_out, h->canal_taps, sizeof(double) * (size_t)n_steps * nc,
+                                cudaMemcpyDeviceToHost, s));
+    long long bad[2] = {0, 0};
+    TF_CUDA(cudaMemcpyAsync(bad, h->bad, sizeof(bad), cudaMemcpyDeviceToHost, s));
+    TF_CUDA(cudaStreamSynchronize(s));
+    if (bad_out) {
+        const long long none = 0x7fffffffffffffffLL;
+        bad_out[0] = bad[0] == none ? -1 : bad[0];
+        bad_out[1] = bad[1] == none ? -1 : bad[1];
+    }
+    return 0;
+}
+
+extern "C" int tf_chan_get(tf_handle h, int which, double* host_out) {
+    TF_TRY(use_device(h));
+    TF_CHECK(h->chan_ready, "tf_chan_get: call tf_chan_init first");
+    TF_CHECK(host_out != nullptr, "tf_chan_get: host_out is NULL");
+    TF_CHECK(which >= 0 && which < TF_F_COUNT, "tf_chan_get: unknown field %d", which);
+    const Geom& g = h->g;
+    switch (which) {
+        case TF_F_VOL: return raster_download<double>(h, h->vol.p, host_out);
+        case TF_F_D: return raster_download<double>(h, h->d.p, host_out);
+        case TF_F_U: return raster_download<double>(h, h->u.p, host_out);
+        case TF_F_Q: return raster_download<double>(h, h->Qcur, host_out);
+        case TF_F_QNEXT: return raster_download<double>(h, h->Qnext, host_out);
+        default: break;
+    }
+    if (!h->scratch64) TF_CUDA(cudaMalloc((void**)&h->scratch64, sizeof(double) * (size_t)g.n_alloc));
+    if (h->state_dirty) {   // mutation flags not built yet: nothing has fired
+        TF_CUDA(cudaMemsetAsync(h->mstate.base, 0, (size_t)g.n_alloc, h->stream));
+    }
+    ChanArgs a = chan_args(h, 0, g.ny);
+    double* out = h->scratch64 + g.origin;
+    dim3 blk(64, 4), grd((g.nx + 63) / 64, (g.ny + 3) / 4);
+    TF_DISPATCH(h, (k_derive<P, L><<<grd, blk, 0, h->stream>>>(a, which, h->wave, out)));
+    TF_CUDA(cudaGetLastError());
+    return raster_download<double>(h, out, host_out);
+}
+
+extern "C" int tf_chan_minmax(tf_handle h, double* out6) {
+    TF_TRY(use_device(h));
+    TF_CHECK(h->chan_ready, "tf_chan_minmax: call tf_chan_init first");
+    TF_CHECK(out6 != nullptr, "tf_chan_minmax: out6 is NULL");
+    const Geom& g = h->g;
+    if (h->partial_cap < 6 * g.ny) {
+        if (h->partial) cudaFree(h->partial);
+        h->partial_cap = 6 * g.ny;
+        TF_CUDA(cudaMalloc((void**)&h->partial, sizeof(double) * h->partial_cap));
+    }
+    ChanArgs a = chan_args(h, 0, g.ny);
+    k_minmax<<<g.ny, 256, 0, h->stream>>>(a, h->partial);
+    TF_CUDA(cudaGetLastError());
+    std::vector<double> part((size_t)6 * g.ny);
+    TF_CUDA(cudaMemcpyAsync(part.data(), h->partial, sizeof(double) * part.size(), cudaMemcpyDeviceToHost, h->stream));
+    TF_CUDA(cudaStreamSynchronize(h->stream));
+    for (int f = 0; f < 6; ++f) {
+        double r = (f & 1) ? -INFINITY : INFINITY;
+        bool nan_seen = false;
+        for (int y = 0; y < g.ny; ++y) {
+            const double v = part[(size_t)6 * y + f];
+            if (v != v) nan_seen = true;
+            else r = (f & 1) ? (v > r ? v : r) : (v < r ? v : r);
+        }
+        out6[f] = nan_seen ? NAN : r;
+    }
+    return 0;
+}
+
+static double layout_bytes_per_cell(tf_handle h) {
+    // bytes the step kernels address per cell-update in the current layout
+    double b = 0.0;
+    const double shape = h->packed ? (4 + 4 + 1) : (8 + 8 + 8 + 8);   // w, ds, angle
+    const double sr = h->packed ? 8 : 16;                            // S, roughness
+    const double R = h->R_is_grid ? 8 : 0;
+    if (h->wave == TF_KINEMATIC) {
+        b = 8 /*Q*/ + 8 /*vol r*/ + 1 + 1 + 1 /*code, mask, mstate*/ + shape + 4 /*dw*/ + sr + R
+            + 32 /*vol, d, u, Qnext w*/;
+    } else {
+        const double A = 8 + 8 + 3 + shape + 4 + R + 16;              // phase A
+        double B = 8 /*d*/ + 2 + shape + 4 + sr + 24;                 // phase B: sfree, u, Qn
+        if (h->wave == TF_DYNAMIC) B += 8 + 8 + 8 + 1;                // Q, vol, u_old, mask
+        b = A + B;
+    }
+    return b;
+}
+
+extern "C" int tf_chan_timing(tf_handle h, double* out4) {
+    TF_TRY(use_device(h));
+    TF_CHECK(out4 != nullptr, "tf_chan_timing: out4 is NULL");
+    if (h->timing_open) {
+        TF_CUDA(cudaEventRecord(h->t1, h->stream));
+        TF_CUDA(cudaEventSynchronize(h->t1));
+        float ms = 0.f;
+        TF_CUDA(cudaEventElapsedTime(&ms, h->t0, h->t1));
+        h->acc_ms += ms;
+        h->timing_open = false;
+    }
+    out4[0] = h->acc_ms;
+    out4[1] = (double)h->acc_steps;
+    out4[2] = (double)h->acc_launches;
+    out4[3] = h->chan_ready ? layout_bytes_per_cell(h) : 0.0;
+    h->acc_ms = 0.0; h->acc_steps = 0; h->acc_launches = 0;
+    return 0;
+}
+
+int chan_free(tf_handle h) {
+    raster_free(h->vol); raster_free(h->d); raster_free(h->u); raster_free(h->u2);
+    raster_free(h->Qa); raster_free(h->Qb); raster_free(h->R); raster_free(h->sfree);
+    raster_free(h->f); raster_free(h->mstate);
+    raster_free(h->w64); raster_free(h->tan64); raster_free(h->cos64);
+    raster_free(h->S64); raster_free(h->n64); raster_free(h->ds64);
+    raster_free(h->w32); raster_free(h->S32); raster_free(h->n32); raster_free(h->ds32);
+    raster_free(h->aidx);
+    void* ptrs[] = {h->lut, h->ds_rows, h->da_rows, h->outlet_idx, h->taps, h->canal_taps,
+                    h->partial, h->scratch64, h->pts_tmp};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    h->lut = nullptr; h->ds_rows = nullptr; h->da_rows = nullptr; h->outlet_idx = nullptr;
+    h->taps = nullptr; h->canal_taps = nullptr; h->partial = nullptr; h->scratch64 = nullptr;
+    h->pts_tmp = nullptr;
+    for (int k = 0; k < 4; ++k) {
+        if (h->pts[k].idx) cudaFree(h->pts[k].idx);
+        if (h->pts[k].val) cudaFree(h->pts[k].val);
+        h->pts[k] = PointSet();
+    }
+    h->chan_ready = false;
+    return 0;
+}

@@ -1,0 +1,175 @@
+// tf_common.cuh -- handle layout, device-grid geometry and error plumbing
+// shared by the D8, routing and communication translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+
+#include "../../include/topoflow_b200.h"
+
+// ---------------------------------------------------------------------------
+// Device grid geometry.
+//
+// Every device raster shares one layout: (ny + 2) rows of `pitch` elements,
+// pitch = nx rounded up to 32, preceded and followed by 32 guard elements.
+// Row -1 and row ny are apron rows (the neighbour strip's edge row, or zeros
+// at a global border), so a kernel may address (y-1 .. y+1, x-1 .. x+1) of
+// any owned cell without bounds tests: x = -1 lands in the previous row's
+// padding (or, when pitch == nx, on the previous row's last cell, which is a
+// border cell with flow code 0 and never contributes).  All row starts are
+// 32-element aligned, so 128-bit loads are always legal.
+// ---------------------------------------------------------------------------
+struct Geom {
+    int nx, ny;          // owned cells
+    int pitch;           // elements per row
+    int64_t n_alloc;     // elements per raster incl. aprons and guards
+    int64_t origin;      // element offset of cell (0, 0)
+    int row_offset;      // first owned row in the global grid
+    int global_ny;       // rows of the global grid
+    int has_north, has_south;   // a neighbour strip exists on that side
+};
+
+static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+#define TF_GUARD 32
+#define TF_STR2(x) #x
+#define TF_STR(x) TF_STR2(x)
+
+// ---------------------------------------------------------------------------
+// Error handling
+// ---------------------------------------------------------------------------
+void tf_set_error(const char* fmt, ...);
+
+#define TF_CUDA(call)                                                          \
+    do {                                                                       \
+        cudaError_t e_ = (call);                                               \
+        if (e_ != cudaSuccess) {                                               \
+            tf_set_error("%s failed at %s:%d: %s", #call, __FILE__, __LINE__,  \
+                         cudaGetErrorString(e_));                              \
+            return 1;                                                          \
+        }                                                                      \
+    } while (0)
+
+#define TF_CHECK(cond, ...)                                                    \
+    do {                                                                       \
+        if (!(cond)) {                                                         \
+            tf_set_error(__VA_ARGS__);                                         \
+            return 1;                                                          \
+        }                                                                      \
+    } while (0)
+
+#define TF_TRY(call)                                                           \
+    do {                                                                       \
+        int r_ = (call);                                                       \
+        if (r_) return r_;                                                     \
+    } while (0)
+
+// ---------------------------------------------------------------------------
+// Typed device raster
+// ---------------------------------------------------------------------------
+template <typename T>
+struct Raster {
+    T* base = nullptr;   // allocation start
+    T* p = nullptr;      // pointer to cell (0, 0)
+};
+
+struct PointSet {
+    int n = 0;
+    int64_t* idx = nullptr;   // device: element offsets relative to cell (0,0)
+    double* val = nullptr;    // device
+};
+
+struct HostParam {
+    std::vector<double> grid;   // dense ny*nx, empty when scalar
+    double scalar = 0.0;
+    int is_grid = 0;            // grid-typed in the reference
+    bool set = false;
+};
+
+struct NcclApi;   // tf_comm.cu
+
+struct tf_handle_s {
+    int device = 0;
+    Geom g{};
+    cudaStream_t stream = nullptr;        // main stream
+    cudaStream_t stream_edge = nullptr;   // boundary rows + halo exchange
+    cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_edge = nullptr, ev_main = nullptr;
+
+    // ---- D8 -------------------------------------------------------------
+    Raster<float> dem;            // DEM, float32
+    Raster<int16_t> raw, raw2;    // working codes (Jacobi pair for link_flats)
+    Raster<uint8_t> code;         // final D8 codes
+    Raster<uint8_t> inmask;       // bit k: child in the k-th add direction
+    Raster<int32_t> parent;       // parent_ID_grid (global calendar IDs)
+    Raster<float> ds0, dw;        // flow length / width (float32)
+    Raster<float> area;           // contributing area
+    Raster<int32_t> pending;      // area: children still to finish
+    float *dx = nullptr, *dy = nullptr, *dd = nullptr;   // per-row, float32
+    bool have_d8 = false, have_area = false;
+    int lr_periodic = 0, tb_periodic = 0;
+    unsigned long long* counters = nullptr;   // device scratch counters [16]
+
+    // ---- routing ----------------------------------------------------------
+    HostParam hp[TF_P_COUNT];
+    int wave = 0, law = 0, packed = 0;
+    int mut_width = 0, mut_angle = 0;
+    double dt = 0.0, rho = 1000.0;
+    bool state_dirty = true;              // mstate must be rebuilt from d
+    double* da_rows = nullptr;            // device [ny + 2] (index y + 1)
+    bool chan_ready = false;
+    // state
+    Raster<double> vol, d, u, u2, Qa, Qb, R, sfree, f;
+    double *Qcur = nullptr, *Qnext = nullptr;   // -> Qa.p / Qb.p
+    double *ucur = nullptr, *unext = nullptr;   // dynamic wave double buffer
+    bool R_is_grid = false;
+    double R_scalar = 0.0;
+    Raster<uint8_t> mstate;               // bit0 mutated, bit1 pending
+    // parameters, generic layout (float64)
+    Raster<double> w64, tan64, cos64, S64, n64, ds64;
+    // parameters, packed layout (float32 + angle table)
+    Raster<float> w32, S32, n32, ds32;
+    Raster<uint8_t> aidx;
+    double* lut = nullptr;                // device [2*256]: tan, cos
+    float* ds_rows = nullptr;             // device [3*(ny+2)]: diag, ew, ns
+    // outlets, diversions
+    int n_outlets = 0;
+    int64_t* outlet_idx = nullptr;        // device
+    std::vector<int64_t> outlet_idx_h;
+    PointSet pts[4];
+    double* pts_tmp = nullptr;            // staging for the diversion kernel
+    int pts_tmp_cap = 0;
+    double* taps = nullptr;               // device ring [cap][n_outlets][4]
+    double* canal_taps = nullptr;         // device [cap][n_canals]
+    int taps_cap = 0;
+    long long* bad = nullptr;             // device [2]
+    double* partial = nullptr;            // device scratch for reductions
+    int partial_cap = 0;
+    double* scratch64 = nullptr;          // one raster for derived fields
+    // timing
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
+    bool timing_open = false;
+    double acc_ms = 0.0;
+    long long acc_steps = 0, acc_launches = 0;
+
+    // ---- communication ------------------------------------------------------
+    void* nccl_comm = nullptr;
+    int rank = 0, nranks = 1;
+};
+
+// helpers implemented in tf_api.cu
+template <typename T> int raster_alloc(tf_handle h, Raster<T>& r, int fill_byte);
+template <typename T> void raster_free(Raster<T>& r);
+template <typename T> int raster_upload(tf_handle h, Raster<T>& r, const T* host);
+template <typename T> int raster_download(tf_handle h, const T* dev_p, T* host);
+int use_device(tf_handle h);
+
+// implemented per TU
+int d8_free(tf_handle h);
+int chan_free(tf_handle h);
+int comm_free(tf_handle h);
+int comm_exchange_rows(tf_handle h, cudaStream_t s, void* const* arrays,
+                       const size_t* elem_sizes, int n_arrays);
+int comm_allreduce_u64(tf_handle h, cudaStream_t s, unsigned long long* dev, int n);
