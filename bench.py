@@ -113,35 +113,62 @@ def build_strip(args, rank, nranks, device, unique_id=None):
 # clocks during the timed region
 # ---------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
-         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
-         'clocks_event_reasons.sw_power_cap')
+    """SM clock and throttle reasons while the timed region runs (NVML in
+    process, every 5 ms; the nvidia-smi line of B200_PROFILING.md is the
+    fallback)."""
+    REASONS = (('hw_slowdown', 0x8), ('sw_power_cap', 0x4), ('hw_thermal_slowdown', 0x40),
+               ('sw_thermal_slowdown', 0x20))
 
     def __init__(self, device):
         super().__init__(daemon=True)
-        self.device, self.rows, self.stop_flag = device, [], False
+        self.device, self.sm, self.mask, self.stop_flag = device, [], 0, False
+        self.sm_max, self.nvml, self.h = None, None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get('CUDA_VISIBLE_DEVICES')
+            idx = int(vis.split(',')[device]) if vis and vis.split(',')[device].isdigit() else device
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+        except Exception as e:                      # noqa: BLE001
+            log('NVML unavailable (%s); falling back to nvidia-smi' % e)
+
+    def _sample(self):
+        if self.nvml is not None:
+            n = self.nvml
+            self.sm.append(float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM)))
+            self.mask |= int(n.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+            time.sleep(0.005)
+            return
+        q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.sw_power_cap,'
+             'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown')
+        out = subprocess.run(['nvidia-smi', '-i', str(self.device), '--query-gpu=' + q,
+                              '--format=csv,noheader,nounits'], capture_output=True, text=True,
+                             timeout=5).stdout.strip()
+        if out:
+            r = [x.strip() for x in out.split(',')]
+            self.sm.append(float(r[0]))
+            self.sm_max = float(r[1])
+            for i, (_, bit) in enumerate(self.REASONS):
+                if r[2 + i] == 'Active':
+                    self.mask |= bit
 
     def run(self):
         while not self.stop_flag:
             try:
-                out = subprocess.run(['nvidia-smi', '-i', str(self.device), '--query-gpu=' + self.Q,
-                                      '--format=csv,noheader,nounits'], capture_output=True,
-                                     text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(',')])
-            except Exception:
-                pass
-            time.sleep(0.2)
+                self._sample()
+            except Exception:                       # noqa: BLE001
+                time.sleep(0.05)
 
     def summary(self):
         self.stop_flag = True
-        if not self.rows:
-            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
-        sm = sorted(float(r[0]) for r in self.rows)
-        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        reasons = [n for i, n in enumerate(names) if any(r[2 + i] == 'Active' for r in self.rows)]
-        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': float(self.rows[0][1]),
-                'reasons': reasons, 'samples': len(sm)}
+        self.join(timeout=6)
+        if not self.sm:
+            return {'sm_mhz': None, 'sm_max_mhz': self.sm_max, 'reasons': ['no sample taken']}
+        sm = sorted(self.sm)
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_min_mhz': sm[0], 'sm_max_mhz': self.sm_max,
+                'reasons': [n for n, bit in self.REASONS if self.mask & bit], 'samples': len(sm)}
 
 
 # ---------------------------------------------------------------------------
@@ -248,7 +275,6 @@ def run_gpu(args):
     s.sync()
     D.barrier()
     wall_ms = (time.perf_counter() - t0) * 1e3
-    clocks = sampler.summary()
     ms = D.max(ms_dev)
     value = cells * D.world * K / (ms * 1e-3)
 
@@ -262,6 +288,7 @@ def run_gpu(args):
     D.barrier()
     e2e_s = D.max(time.perf_counter() - t0)
     e2e = cells * D.world * Ke / e2e_s
+    clocks = sampler.summary()
     assert bad[0] == -1 and bad[1] == -1, 'bad depth / velocity flagged: %s' % bad
     s.timing()
 

@@ -100,6 +100,12 @@ def test_three_waves_match_oracle(wave, packed):
         for name, fid in (('f', L.F_F), ('Rh', L.F_RH), ('A_wet', L.F_A_WET),
                           ('P_wet', L.F_P_WET), ('tau', L.F_TAU), ('u_star', L.F_U_STAR),
                           ('froude', L.F_FROUDE), ('S_free', L.F_S_FREE), ('width', L.F_WIDTH)):
+            if name == 'S_free' and wave == 'kinematic':
+                # never updated by the kinematic wave: the component keeps the
+                # host copy made at channels_base.py:889
+                with pytest.raises(L.TopoflowB200Error, match='kinematic'):
+                    s.get(fid)
+                continue
             assert field_err(s.get(fid), getattr(ch, name)) <= RTOL, name
         mm = s.minmax()
         o = ch.mins_and_maxes()
@@ -152,17 +158,21 @@ def test_generic_layout_when_values_are_not_float32():
 
 
 def test_overbank_rule_fires_like_the_reference():
-    """Heavy rain on narrow channels: top width outgrows the flow width, the
-    cell becomes a rectangle for good (channels_base.py:1449-1454)."""
+    """5 m cells with channels up to 6 m wide: 'top_width > dw' fires for many
+    cells on the very first step and for more as the depth grows; each such
+    cell becomes a rectangle of width dw for good (channels_base.py:1449-1454).
+    (The case is kept hydraulically stable, CFL < 1: with u*dt > ds the
+    reference's own scheme amplifies 1-ulp differences without bound, so no
+    two implementations of it agree there.)"""
     from topoflow_old_b200 import _lib as L
-    c = make_case(64, 64, seed=21, angle_mode='classes', rain_mmph=3000.0)
-    s, ch, _ = run_pair(c, 0, 2.0, 400, check_every=50)
+    c = make_case(64, 64, seed=21, cell=5.0, angle_mode='classes', rain_mmph=400.0)
+    s, ch, _ = run_pair(c, 0, 0.5, 600, check_every=100, batch=25)
     try:
         fired = (ch.angle == 0) & (np.float64(c['angle']) != 0)
-        assert fired.sum() > 20
-        assert np.array_equal(s.get(L.F_MUTATED) == 1.0, ch.width == np.float64(ch.dw)) or \
-            np.array_equal(s.get(L.F_WIDTH), ch.width)
+        assert fired.sum() > 300
         assert np.array_equal(s.get(L.F_WIDTH), ch.width)
+        rule = (ch.width != c['width']) | fired
+        assert np.array_equal(s.get(L.F_MUTATED)[rule], np.ones(int(rule.sum())))
     finally:
         s.close()
 

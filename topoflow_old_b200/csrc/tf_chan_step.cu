@@ -176,6 +176,9 @@ extern "C" int tf_chan_get(tf_handle h, int which, double* host_out) {
         case TF_F_QNEXT: return raster_download<double>(h, h->Qnext, host_out);
         default: break;
     }
+    TF_CHECK(!(which == TF_F_S_FREE && h->wave == TF_KINEMATIC),
+             "tf_chan_get: S_free is not a device field for the kinematic wave (it stays the "
+             "copy of S_bed taken at initialisation, channels_base.py:889)");
     if (!h->scratch64) TF_CUDA(cudaMalloc((void**)&h->scratch64, sizeof(double) * (size_t)g.n_alloc));
     if (h->state_dirty) {   // mutation flags not built yet: nothing has fired
         TF_CUDA(cudaMemsetAsync(h->mstate.base, 0, (size_t)g.n_alloc, h->stream));

@@ -284,7 +284,9 @@ __device__ __forceinline__ float area_of(const D8Args& a, int x, int y, unsigned
         const int j = (k + 4) & 7;
         if ((m >> j) & 1u) {
             int xx = wrap_x(x + c_dc[k], a.nx);
-            acc += __ldcg(&area[(int64_t)(y + c_dr[k]) * a.pitch + xx]);
+            int yy = y + c_dr[k];                             // "%" wrap, :1105-1108
+            if (yy < 0) yy += a.ny; else if (yy >= a.ny) yy -= a.ny;
+            acc += __ldcg(&area[(int64_t)yy * a.pitch + xx]);
         }
     }
     return acc;
