@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libtopoflow_b200.so')
+LIB_PATH = os.environ.get('TF_B200_LIB') or os.path.join(_HERE, 'libtopoflow_b200.so')
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(

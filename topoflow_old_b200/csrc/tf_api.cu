@@ -1,5 +1,6 @@
 // tf_api.cu -- handle lifetime, error reporting and raster transfer helpers.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include "tf_common.cuh"
 
@@ -98,6 +99,7 @@ extern "C" int tf_create(int nx, int ny, int device, unsigned flags,
     (void)flags;
     tf_handle h = new tf_handle_s();
     h->device = device;
+    { const char* e = getenv("TF_B200_DEBUG_SYNC"); h->debug_sync = e && e[0] == '1'; }
     Geom& g = h->g;
     g.nx = nx;
     g.ny = ny;

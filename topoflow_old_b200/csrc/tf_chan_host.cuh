@@ -30,7 +30,7 @@ static inline ChanArgs chan_args(tf_handle h, int y_begin, int y_end) {
 }
 
 static inline dim3 tile_grid(const Geom& g, int rows) {
-    return dim3((g.pitch / 4 + 31) / 32, (rows + 7) / 8);
+    return dim3((g.pitch / CPT + 31) / 32, (rows + 7) / 8);
 }
 
 // PACKED x LAW dispatch

@@ -14,6 +14,10 @@
 #pragma once
 #include "tf_chan_math.cuh"
 
+#ifndef TF_MINBLOCKS
+#define TF_MINBLOCKS 6
+#endif
+
 struct ChanArgs {
     int nx, ny, pitch;
     int y_begin, y_end;            // rows this launch covers
@@ -47,15 +51,15 @@ struct ChanArgs {
 
 // ---------------------------------------------------------------------------
 template <bool PACKED>
-__device__ __forceinline__ void load_shape(const ChanArgs& a, int64_t i, double (&w)[4],
-                                           double (&t)[4], double (&c)[4], double (&ds)[4]) {
+__device__ __forceinline__ void load_shape(const ChanArgs& a, int64_t i, double (&w)[CPT],
+                                           double (&t)[CPT], double (&c)[CPT], double (&ds)[CPT]) {
     if (PACKED) {
         ld4(a.w32 + i, w);
         ld4(a.ds32 + i, ds);
-        int ai[4];
+        int ai[CPT];
         ld4(a.aidx + i, ai);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < CPT; ++k) {
             t[k] = __ldg(a.lut + ai[k]);
             c[k] = __ldg(a.lut + 256 + ai[k]);
         }
@@ -68,8 +72,8 @@ __device__ __forceinline__ void load_shape(const ChanArgs& a, int64_t i, double 
 }
 
 template <bool PACKED>
-__device__ __forceinline__ void load_slope_rough(const ChanArgs& a, int64_t i, double (&S)[4],
-                                                 double (&n)[4]) {
+__device__ __forceinline__ void load_slope_rough(const ChanArgs& a, int64_t i, double (&S)[CPT],
+                                                 double (&n)[CPT]) {
     if (PACKED) {
         ld4(a.S32 + i, S);
         ld4(a.n32 + i, n);
@@ -108,28 +112,28 @@ __device__ __forceinline__ void flag_bad(const ChanArgs& a, int which, int x, in
 // ---------------------------------------------------------------------------
 template <bool PACKED>
 __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int y, int64_t i,
-                                                 double (&Q)[4], double (&v)[4], double (&d)[4],
-                                                 double (&w)[4], double (&t)[4], double (&c)[4],
-                                                 double (&ds)[4], double (&dwv)[4], int (&code)[4],
-                                                 int (&m)[4]) {
-    int mask[4], ms[4];
+                                                 double (&Q)[CPT], double (&v)[CPT], double (&d)[CPT],
+                                                 double (&w)[CPT], double (&t)[CPT], double (&c)[CPT],
+                                                 double (&ds)[CPT], double (&dwv)[CPT], int (&code)[CPT],
+                                                 int (&m)[CPT], int (&ms)[CPT]) {
+    int mask[CPT];
     ld4(a.Q + i, Q);
     ld4c(a.vol + i, v);
     ld4(a.code + i, code);
     ld4(a.inmask + i, mask);
-    {
-        const uchar4 s = *reinterpret_cast<const uchar4*>(a.mstate + i);
-        ms[0] = s.x; ms[1] = s.y; ms[2] = s.z; ms[3] = s.w;
-    }
+    ld4c(a.mstate + i, ms);
     load_shape<PACKED>(a, i, w, t, c, ds);
     ld4(a.dw + i, dwv);
-    double R[4];
+    double R[CPT];
     if (a.Rgrid) ld4(a.Rgrid + i, R);
-    else { R[0] = R[1] = R[2] = R[3] = a.Rs; }
+    else {
+#pragma unroll
+        for (int k = 0; k < CPT; ++k) R[k] = a.Rs;
+    }
     const double da = a.da_rows[y];
     const double dt = a.dt;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < CPT; ++k) {
         m[k] = (ms[k] & 1) | ((ms[k] >> 1) & 1);
         apply_overbank(a, m[k], dwv[k], w[k], t[k], c[k]);
         double acc = v[k] + (R[k] * da) * dt;                  // :1334
@@ -151,38 +155,39 @@ __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int 
 
 // next step's overbank test with this step's depth (:1449-1450), packed into
 // the state byte; written only when it changes
-__device__ __forceinline__ void store_mstate(const ChanArgs& a, int64_t i, const int (&m)[4],
-                                             const double (&d)[4], const double (&w)[4],
-                                             const double (&t)[4], const double (&dwv)[4]) {
-    const uchar4 old = *reinterpret_cast<const uchar4*>(a.mstate + i);
-    unsigned char nw[4];
+__device__ __forceinline__ void store_mstate(const ChanArgs& a, int64_t i, const int (&ms)[CPT],
+                                             const int (&m)[CPT], const double (&d)[CPT],
+                                             const double (&w)[CPT], const double (&t)[CPT],
+                                             const double (&dwv)[CPT]) {
+    int nw[CPT];
+    bool changed = false;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < CPT; ++k) {
         const double top = w[k] + ((2.0 * d[k]) * t[k]);
-        nw[k] = (unsigned char)(m[k] | ((top > dwv[k]) ? 2 : 0));
+        nw[k] = m[k] | ((top > dwv[k]) ? 2 : 0);
+        changed = changed || (nw[k] != ms[k]);
     }
-    if (nw[0] != old.x || nw[1] != old.y || nw[2] != old.z || nw[3] != old.w)
-        *reinterpret_cast<uchar4*>(a.mstate + i) = make_uchar4(nw[0], nw[1], nw[2], nw[3]);
+    if (changed) st4(a.mstate + i, nw);
 }
 
 // ---------------------------------------------------------------------------
 // kinematic wave: the whole step in one pass
 // ---------------------------------------------------------------------------
 template <bool PACKED, int LAW>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, TF_MINBLOCKS)
 k_step_kinematic(const ChanArgs a) {
-    const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
     const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
     if (x4 >= a.pitch || y >= a.y_end) return;
     const int64_t i = (int64_t)y * a.pitch + x4;
-    double Q[4], v[4], d[4], w[4], t[4], c[4], ds[4], dwv[4], S[4], n[4], u[4], Qn[4];
-    int code[4], m[4];
-    volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m);
+    double Q[CPT], v[CPT], d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT], S[CPT], n[CPT], u[CPT], Qn[CPT];
+    int code[CPT], m[CPT], ms[CPT];
+    volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
     load_slope_rough<PACKED>(a, i, S, n);
     bool bad_d = false, bad_u = false;
     int bx = 0;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < CPT; ++k) {
         const bool noflow = (code[k] == 0);
         const XSection xs = chan_xsection(d[k], w[k], t[k], c[k], noflow);
         double uu = chan_velocity<LAW>(xs.Rh, S[k], n[k], d[k]);   // kinematic: S = S_bed
@@ -198,11 +203,11 @@ k_step_kinematic(const ChanArgs a) {
     st4(a.d + i, d);
     st4(a.u + i, u);
     st4(a.Qn + i, Qn);
-    store_mstate(a, i, m, d, w, t, dwv);
+    store_mstate(a, i, ms, m, d, w, t, dwv);
     if (bad_d || bad_u) {
         // report the first offending cell of each kind in this segment
 #pragma unroll
-        for (int k = 3; k >= 0; --k) {
+        for (int k = CPT - 1; k >= 0; --k) {
             if (x4 + k < a.nx) {
                 if (bad_value(d[k])) flag_bad(a, 0, x4 + k, y);
                 if (bad_value(u[k])) flag_bad(a, 1, x4 + k, y);
@@ -218,17 +223,17 @@ k_step_kinematic(const ChanArgs a) {
 template <bool PACKED>
 __global__ void __launch_bounds__(256)
 k_phase_a(const ChanArgs a) {
-    const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
     const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
     if (x4 >= a.pitch || y >= a.y_end) return;
     const int64_t i = (int64_t)y * a.pitch + x4;
-    double Q[4], v[4], d[4], w[4], t[4], c[4], ds[4], dwv[4];
-    int code[4], m[4];
-    volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m);
+    double Q[CPT], v[CPT], d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT];
+    int code[CPT], m[CPT], ms[CPT];
+    volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
     st4(a.vol + i, v);
     st4(a.d + i, d);
-    store_mstate(a, i, m, d, w, t, dwv);
+    store_mstate(a, i, ms, m, d, w, t, dwv);
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
+    for (int k = 0; k < CPT; ++k)
         if (x4 + k < a.nx && bad_value(d[k])) flag_bad(a, 0, x4 + k, y);
 }

@@ -26,23 +26,20 @@ __device__ __forceinline__ double free_slope(const ChanArgs& a, int64_t idx, int
 template <bool PACKED, int LAW, int WAVE>
 __global__ void __launch_bounds__(256)
 k_phase_b(const ChanArgs a) {
-    const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
     const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
     if (x4 >= a.pitch || y >= a.y_end) return;
     const int64_t i = (int64_t)y * a.pitch + x4;
-    double d[4], w[4], t[4], c[4], ds[4], dwv[4], S[4], n[4], u[4], Qn[4], sf[4];
-    int code[4], ms[4];
+    double d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT], S[CPT], n[CPT], u[CPT], Qn[CPT], sf[CPT];
+    int code[CPT], ms[CPT];
     ld4c(a.d + i, d);
     ld4(a.code + i, code);
-    {
-        const uchar4 s = *reinterpret_cast<const uchar4*>(a.mstate + i);
-        ms[0] = s.x; ms[1] = s.y; ms[2] = s.z; ms[3] = s.w;
-    }
+    ld4c(a.mstate + i, ms);
     load_shape<PACKED>(a, i, w, t, c, ds);
     ld4(a.dw + i, dwv);
     load_slope_rough<PACKED>(a, i, S, n);
-    double Q[4], v[4], uo[4];
-    int mask[4];
+    double Q[CPT], v[CPT], uo[CPT];
+    int mask[CPT];
     if (WAVE == 2) {
         ld4(a.Q + i, Q);
         ld4c(a.vol + i, v);
@@ -50,7 +47,7 @@ k_phase_b(const ChanArgs a) {
         ld4(a.inmask + i, mask);
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < CPT; ++k) {
         const bool noflow = (code[k] == 0);
         apply_overbank(a, ms[k] & 1, dwv[k], w[k], t[k], c[k]);
         const XSection xs = chan_xsection(d[k], w[k], t[k], c[k], noflow);
@@ -161,21 +158,21 @@ static __global__ void k_diversions(PointsArgs p, double* Q, double* vol, double
 template <bool PACKED>
 __global__ void __launch_bounds__(256)
 k_init_mstate(const ChanArgs a) {
-    const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
     const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
     if (x4 >= a.pitch || y >= a.y_end) return;
     const int64_t i = (int64_t)y * a.pitch + x4;
-    double d[4], w[4], t[4], c[4], ds[4], dwv[4];
+    double d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT];
     ld4c(a.d + i, d);
     load_shape<PACKED>(a, i, w, t, c, ds);
     ld4(a.dw + i, dwv);
-    unsigned char nw[4];
+    int nw[CPT];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < CPT; ++k) {
         const double top = w[k] + ((2.0 * d[k]) * t[k]);
         nw[k] = (top > dwv[k]) ? 2 : 0;
     }
-    *reinterpret_cast<uchar4*>(a.mstate + i) = make_uchar4(nw[0], nw[1], nw[2], nw[3]);
+    st4(a.mstate + i, nw);
 }
 
 // ---------------------------------------------------------------------------

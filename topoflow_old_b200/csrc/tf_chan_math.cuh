@@ -41,7 +41,7 @@ __device__ __forceinline__ XSection chan_xsection(double d, double w, double t, 
     XSection s;
     const double L2 = d * t;
     s.A_wet = d * (w + L2);
-    s.P_wet = w + ((2.0 * d) / c);
+    s.P_wet = (c == 1.0) ? (w + (2.0 * d)) : (w + ((2.0 * d) / c));   // x / 1 is exact
     if (noflow) s.P_wet = 1.0;
     s.Rh = s.A_wet / s.P_wet;
     if (noflow) s.Rh = 0.0;
@@ -85,27 +85,79 @@ __device__ __forceinline__ bool bad_value(double v) {
     return (v < 0.0) || !isfinite(v);                        // :1992, :2044
 }
 
-// ---- 4-wide row segment loads / stores --------------------------------------
-__device__ __forceinline__ void ld4(const double* __restrict__ p, double (&o)[4]) {
-    const double2 a = __ldg(reinterpret_cast<const double2*>(p));
-    const double2 b = __ldg(reinterpret_cast<const double2*>(p) + 1);
-    o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+// ---- CPT-wide row segment loads / stores (CPT = cells per thread) --------------
+#ifndef TF_CPT
+#define TF_CPT 2
+#endif
+#define CPT TF_CPT
+static_assert(CPT == 1 || CPT == 2 || CPT == 4, "cells per thread must be 1, 2 or 4");
+
+template <typename V, typename T, bool NC>
+__device__ __forceinline__ V ldv(const T* p) {
+    if (NC) return __ldg(reinterpret_cast<const V*>(p));
+    return *reinterpret_cast<const V*>(p);
 }
-__device__ __forceinline__ void ld4(const float* __restrict__ p, double (&o)[4]) {
+
+template <bool NC>
+__device__ __forceinline__ void ld_f64(const double* p, double (&o)[CPT]) {
+#if TF_CPT == 1
+    o[0] = ldv<double, double, NC>(p);
+#else
+    const double2 a = ldv<double2, double, NC>(p);
+    o[0] = a.x; o[1] = a.y;
+#if TF_CPT == 4
+    const double2 b = ldv<double2, double, NC>(p + 2);
+    o[2] = b.x; o[3] = b.y;
+#endif
+#endif
+}
+template <bool NC>
+__device__ __forceinline__ void ld_u8(const uint8_t* p, int (&o)[CPT]) {
+#if TF_CPT == 1
+    o[0] = ldv<unsigned char, uint8_t, NC>(p);
+#elif TF_CPT == 2
+    const uchar2 a = ldv<uchar2, uint8_t, NC>(p);
+    o[0] = a.x; o[1] = a.y;
+#else
+    const uchar4 a = ldv<uchar4, uint8_t, NC>(p);
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w;
+#endif
+}
+// read-only (non-coherent) path: rasters no kernel of this step writes
+__device__ __forceinline__ void ld4(const double* __restrict__ p, double (&o)[CPT]) { ld_f64<true>(p, o); }
+__device__ __forceinline__ void ld4(const uint8_t* __restrict__ p, int (&o)[CPT]) { ld_u8<true>(p, o); }
+__device__ __forceinline__ void ld4(const float* __restrict__ p, double (&o)[CPT]) {
+#if TF_CPT == 1
+    o[0] = __ldg(p);
+#elif TF_CPT == 2
+    const float2 a = __ldg(reinterpret_cast<const float2*>(p));
+    o[0] = a.x; o[1] = a.y;
+#else
     const float4 a = __ldg(reinterpret_cast<const float4*>(p));
     o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w;
+#endif
 }
-__device__ __forceinline__ void ld4(const uint8_t* __restrict__ p, int (&o)[4]) {
-    const uchar4 a = __ldg(reinterpret_cast<const uchar4*>(p));
-    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w;
-}
-// plain (coherent) loads for buffers another kernel of the same step wrote
-__device__ __forceinline__ void ld4c(const double* p, double (&o)[4]) {
-    const double2 a = *reinterpret_cast<const double2*>(p);
-    const double2 b = *(reinterpret_cast<const double2*>(p) + 1);
-    o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
-}
-__device__ __forceinline__ void st4(double* p, const double (&v)[4]) {
+// plain (coherent) loads for buffers this kernel, or an earlier kernel of the
+// same step, writes
+__device__ __forceinline__ void ld4c(const double* p, double (&o)[CPT]) { ld_f64<false>(p, o); }
+__device__ __forceinline__ void ld4c(const uint8_t* p, int (&o)[CPT]) { ld_u8<false>(p, o); }
+
+__device__ __forceinline__ void st4(double* p, const double (&v)[CPT]) {
+#if TF_CPT == 1
+    p[0] = v[0];
+#else
     reinterpret_cast<double2*>(p)[0] = make_double2(v[0], v[1]);
+#if TF_CPT == 4
     reinterpret_cast<double2*>(p)[1] = make_double2(v[2], v[3]);
+#endif
+#endif
+}
+__device__ __forceinline__ void st4(uint8_t* p, const int (&v)[CPT]) {
+#if TF_CPT == 1
+    p[0] = (uint8_t)v[0];
+#elif TF_CPT == 2
+    *reinterpret_cast<uchar2*>(p) = make_uchar2(v[0], v[1]);
+#else
+    *reinterpret_cast<uchar4*>(p) = make_uchar4(v[0], v[1], v[2], v[3]);
+#endif
 }

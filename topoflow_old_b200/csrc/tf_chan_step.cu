@@ -6,7 +6,7 @@
 static int launch_kinematic(tf_handle h, cudaStream_t s, int y0, int y1) {
     ChanArgs a = chan_args(h, y0, y1);
     TF_DISPATCH(h, (k_step_kinematic<P, L><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a)));
-    TF_CUDA(cudaGetLastError());
+    TF_LAUNCHED(h, s, "k_step_kinematic");
     h->acc_launches++;
     return 0;
 }
@@ -15,7 +15,7 @@ static int launch_phase_a(tf_handle h, cudaStream_t s, int y0, int y1) {
     ChanArgs a = chan_args(h, y0, y1);
     if (h->packed) k_phase_a<true><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a);
     else k_phase_a<false><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a);
-    TF_CUDA(cudaGetLastError());
+    TF_LAUNCHED(h, s, "k_phase_a");
     h->acc_launches++;
     return 0;
 }
@@ -26,7 +26,7 @@ static int launch_phase_b(tf_handle h, cudaStream_t s, int y0, int y1) {
         TF_DISPATCH(h, (k_phase_b<P, L, 1><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a)));
     else
         TF_DISPATCH(h, (k_phase_b<P, L, 2><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a)));
-    TF_CUDA(cudaGetLastError());
+    TF_LAUNCHED(h, s, "k_phase_b");
     h->acc_launches++;
     return 0;
 }
@@ -56,7 +56,7 @@ static int queue_steps(tf_handle h, int n_steps, int record) {
         ChanArgs a = chan_args(h, 0, g.ny);
         if (h->packed) k_init_mstate<true><<<tile_grid(g, g.ny), dim3(32, 8), 0, s>>>(a);
         else k_init_mstate<false><<<tile_grid(g, g.ny), dim3(32, 8), 0, s>>>(a);
-        TF_CUDA(cudaGetLastError());
+        TF_LAUNCHED(h, s, "k_init_mstate");
         h->state_dirty = false;
     }
     if (!h->timing_open) {
@@ -77,7 +77,7 @@ static int queue_steps(tf_handle h, int n_steps, int record) {
             p.tmp = h->pts_tmp;
             p.canals_in_out = (record && h->canal_taps) ? h->canal_taps + (size_t)step * h->pts[TF_PT_CANALS_IN].n : nullptr;
             k_diversions<<<1, 32, 0, s>>>(p, h->Qcur, h->vol.p, h->dt);
-            TF_CUDA(cudaGetLastError());
+            TF_LAUNCHED(h, s, "k_diversions");
             h->acc_launches++;
             if (multi) {   // a diverted cell on an edge row changes the neighbour's halo
                 void* arr[1] = {h->Qcur};
@@ -126,7 +126,7 @@ static int queue_steps(tf_handle h, int n_steps, int record) {
             ChanArgs a = chan_args(h, 0, g.ny);
             double* out = h->taps + (size_t)step * h->n_outlets * 4;
             TF_DISPATCH(h, (k_taps<P, L><<<(h->n_outlets + 63) / 64, 64, 0, s>>>(a, h->outlet_idx, h->n_outlets, out)));
-            TF_CUDA(cudaGetLastError());
+            TF_LAUNCHED(h, s, "k_taps");
             h->acc_launches++;
         }
     }

@@ -61,6 +61,18 @@ void tf_set_error(const char* fmt, ...);
         }                                                                      \
     } while (0)
 
+// after a kernel launch: always catch launch errors; with TF_B200_DEBUG_SYNC=1
+// also wait for the kernel so a device fault is reported against its name
+#define TF_LAUNCHED(h, stream, name)                                           \
+    do {                                                                       \
+        cudaError_t e_ = cudaGetLastError();                                   \
+        if (e_ == cudaSuccess && (h)->debug_sync) e_ = cudaStreamSynchronize(stream); \
+        if (e_ != cudaSuccess) {                                               \
+            tf_set_error("kernel %s: %s", name, cudaGetErrorString(e_));       \
+            return 1;                                                          \
+        }                                                                      \
+    } while (0)
+
 #define TF_TRY(call)                                                           \
     do {                                                                       \
         int r_ = (call);                                                       \
@@ -157,6 +169,7 @@ struct tf_handle_s {
     // ---- communication ------------------------------------------------------
     void* nccl_comm = nullptr;
     int rank = 0, nranks = 1;
+    bool debug_sync = false;              // TF_B200_DEBUG_SYNC=1: sync + check after every launch
 };
 
 // helpers implemented in tf_api.cu
