@@ -212,6 +212,30 @@ int tf_chan_minmax(tf_handle h, double* out6);
  * addressed by the step kernels for the current layout. */
 int tf_chan_timing(tf_handle h, double* out4);
 
+/* sum over an ny x nx device grid of (R*da)*dt -- the vol_R increment that
+ * tf_chan_set_R returns -- for callers that are not allowed to allocate
+ * device memory: code inside a stream capture, plug-ins whose host owns all
+ * GPU memory through its own pool, loops that cannot take the device-wide
+ * stall a cudaMalloc/cudaFree can cause.  This entry point has no counterpart
+ * in the reference; it exists only for such callers.
+ *   R_dev        device pointer, row y starts at R_dev + y*pitch (elements)
+ *   da_rows_dev  device float64 [ny] cell area per row, or NULL to use `da`
+ *   sum_out_dev  device pointer to one float64, written when the stream runs
+ *   stream       a cudaStream_t, or NULL for the default stream
+ * It calls no cudaMalloc / cudaFree and no allocating library routine.  Its
+ * per-row partial sums live in a fixed array inside the library image
+ * (65536 rows x 8 B = 512 KiB per GPU, held until the process exits); a grid
+ * with more rows is refused with an error -- use tf_chan_set_R for those.
+ * The first call on each device looks the array's address up
+ * (cudaGetSymbolAddress); make that first call before any stream capture
+ * starts.  All calls on a device share the one array: two calls whose kernels
+ * can overlap on the GPU (different streams) race on it, so keep them on one
+ * stream or order them with events.  Nothing has to be zeroed between calls:
+ * every slot that is read is overwritten first. */
+int tf_sum_R_noalloc(const double* R_dev, int nx, int ny, long long pitch,
+                     const double* da_rows_dev, double da, double dt,
+                     double* sum_out_dev, void* stream);
+
 /* ---- row-strip decomposition over several GPUs ---------------------------- */
 
 /* 128-byte NCCL unique id for tf_comm_init (rank 0 creates, all ranks use). */

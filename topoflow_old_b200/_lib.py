@@ -53,6 +53,8 @@ SIGNATURES = {
     'tf_chan_get': (C.c_int, [handle_t, C.c_int, _dp]),
     'tf_chan_minmax': (C.c_int, [handle_t, _dp]),
     'tf_chan_timing': (C.c_int, [handle_t, _dp]),
+    'tf_sum_R_noalloc': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_void_p, C.c_double,
+                                   C.c_double, C.c_void_p, C.c_void_p]),
     'tf_comm_unique_id': (C.c_int, [_u8p]),
     'tf_comm_init': (C.c_int, [handle_t, C.c_int, C.c_int, _u8p]),
 }
