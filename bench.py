@@ -69,15 +69,15 @@ def synth_inputs(nx, global_ny, row0, nrows, seed=20170226):
     return dem, north, south, nval, width, angle
 
 
-def build_strip(args, rank, nranks, device, unique_id=None):
+def build_strip(args, rank, nranks, device, unique_id=None, reduce_min=None):
     """D8 grid and routing state of this rank's strip, ready to step."""
     from topoflow_old_b200 import _lib as L
     from topoflow_old_b200.engine import Strip
     from topoflow_old_b200.routing import setup_channels
     from topoflow_old_b200.utils import synth
-    nx, ny = args.size, args.size
-    global_ny = ny * nranks
-    row0 = rank * ny
+    from topoflow_old_b200 import strips
+    nx, global_ny = args.size, args.size * nranks          # weak scaling: size^2 cells per GPU
+    row0, ny = strips.strip_rows(global_ny, nranks, rank)
     t0 = time.time()
     dem, north, south, nval, width, angle = synth_inputs(nx, global_ny, row0, ny)
     log('[rank %d] synthetic inputs %.1fs' % (rank, time.time() - t0))
@@ -103,7 +103,7 @@ def build_strip(args, rank, nranks, device, unique_id=None):
     t0 = time.time()
     setup_channels(s, WAVE_ID[args.wave], L.MANNING, DT[args.wave], CELL * CELL, np.float64(slope),
                    width, angle, np.float64(nval), sinu=1.0, d0=0.0, outlets=outlets,
-                   allow_packed=not args.generic, ds=ds)
+                   allow_packed=not args.generic, ds=ds, reduce_min=reduce_min)
     log('[rank %d] routing setup %.1fs' % (rank, time.time() - t0))
     s.set_R(RAIN_MPS)
     return s
@@ -258,7 +258,8 @@ def run_gpu(args):
     if D.world > 1:
         uid = Strip.comm_unique_id() if D.rank == 0 else np.zeros(128, dtype=np.uint8)
         uid = D.bcast_bytes(uid)
-    s = build_strip(args, D.rank, D.world, D.local_rank, uid)
+    s = build_strip(args, D.rank, D.world, D.local_rank, uid,
+                    reduce_min=(lambda v: -D.max(-v)) if D.world > 1 else None)
     cells = float(args.size) * args.size              # per GPU
     K, W = args.steps, max(args.warmup, 0)
 

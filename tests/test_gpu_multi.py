@@ -1,0 +1,80 @@
+"""Two row strips on two GPUs (one process each, halo rows over NCCL through
+the C ABI) against one strip holding the whole grid: every owned row must be
+bit-identical, for the D8 products and for the routed state."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+NX, NY, STEPS = 200, 192, 60
+
+
+def _n_devices():
+    from topoflow_old_b200.engine import device_count
+    return device_count()
+
+
+def _inputs():
+    from topoflow_old_b200.utils import synth
+    dem = synth.fractal_dem(NX, NY, seed=5, roughness=8.0)
+    dem[60:66, 40:52] = dem[60, 40]                 # a flat straddling nothing in particular
+    dem[94:98, 100:110] = dem[95, 100]              # a flat straddling the strip boundary (row 96)
+    w = np.float64(synth.uniform_field(NX, NY, 1.0, 6.0, seed=6))
+    a = np.float64(synth.class_field(NX, NY, [0.0, 30.0, 45.0], seed=7, block=8)) * (np.pi / 180.0)
+    n = np.float64(synth.uniform_field(NX, NY, 0.03, 0.15, seed=8))
+    return dem, w, a, n
+
+
+def _run_strip(rank, world, uid, wave, out_dir):
+    from topoflow_old_b200 import _lib as L
+    from topoflow_old_b200 import strips
+    from topoflow_old_b200.engine import Strip
+    from topoflow_old_b200.routing import setup_channels
+    from topoflow_old_b200.utils import synth
+    dem, w, a, n = _inputs()
+    r0, nr = strips.strip_rows(NY, world, rank)
+    s = Strip(NX, nr, device=rank if world > 1 else 0)
+    if world > 1:
+        north, south = strips.neighbours(world, rank)
+        s.set_strip(r0, NY, north is not None, south is not None)
+        s.comm_init(rank, world, uid)
+    ones = np.ones(nr, dtype=np.float32)
+    stats = s.d8_build(dem[r0:r0 + nr], 30 * ones, 30 * ones, np.float32(np.sqrt(1800.0)) * ones)
+    code, ds = s.d8_get(L.D8_CODE), s.d8_get(L.D8_DS)
+    sl = lambda g: g[r0:r0 + nr].copy()
+    slope = np.full((nr, NX), 0.01) + 0.001 * np.float64(sl(n))
+    dt = 0.5 if wave == L.DYNAMIC else 2.0
+    setup_channels(s, wave, L.MANNING, dt, 900.0, slope, sl(w), sl(a), sl(n),
+                   outlets=[(nr // 2, NX // 2)], ds=ds)
+    s.set_R(60.0 / 3.6e6)
+    taps, _, bad = s.step(STEPS)
+    assert bad[0] == -1 and bad[1] == -1
+    out = dict(code=code, parent=s.d8_get(L.D8_PARENT_ID), inmask=s.d8_get(L.D8_INMASK),
+               vol=s.get(L.F_VOL), d=s.get(L.F_D), u=s.get(L.F_U), Q=s.get(L.F_Q),
+               stats=np.array([stats['n_flats'], stats['n_pits'], stats['n_reps']]))
+    np.savez(os.path.join(out_dir, 'w%d_r%d_wave%d.npz' % (world, rank, wave)), **out)
+    s.close()
+
+
+def _worker(rank, world, uid, wave, out_dir):
+    _run_strip(rank, world, uid, wave, out_dir)
+
+
+@pytest.mark.parametrize('wave', [0, 1, 2])
+def test_two_gpu_strips_match_single_gpu(tmp_path, wave):
+    if _n_devices() < 2:
+        pytest.skip('needs 2 GPUs')
+    import torch.multiprocessing as mp
+    from topoflow_old_b200.engine import Strip
+    uid = Strip.comm_unique_id()
+    mp.spawn(_worker, args=(2, uid, wave, str(tmp_path)), nprocs=2, join=True)
+    _run_strip(0, 1, None, wave, str(tmp_path))
+    one = np.load(str(tmp_path / ('w1_r0_wave%d.npz' % wave)))
+    parts = [np.load(str(tmp_path / ('w2_r%d_wave%d.npz' % (r, wave)))) for r in range(2)]
+    for key in ('code', 'parent', 'inmask', 'vol', 'd', 'u', 'Q'):
+        got = np.concatenate([p[key] for p in parts], axis=0)
+        assert np.array_equal(got, one[key]), key
+    assert one['Q'].max() > 0
+    assert np.array_equal(parts[0]['stats'], one['stats'])       # all-reduced counters

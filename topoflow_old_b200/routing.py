@@ -13,7 +13,7 @@ from .engine import Strip
 G = np.float64(9.81)
 
 
-def remove_bad_slopes(slope, report=None):
+def remove_bad_slopes(slope, report=None, reduce_min=None):
     """channels_base.py:2675-2754: zero, negative and non-finite slopes take
     the smallest positive slope of the grid.  Returns the float64 grid."""
     wz = (slope == 0.0)
@@ -21,11 +21,17 @@ def remove_bad_slopes(slope, report=None):
     wi = np.logical_not(np.isfinite(slope))
     good = np.invert(np.logical_or(slope <= 0.0, wi))
     nz, nn, ni = int(wz.sum()), int(wn.sum()), int(wi.sum())
-    if (nz + nn + ni) == 0 or not good.any():
+    if reduce_min is None and ((nz + nn + ni) == 0 or not good.any()):
         return slope
-    s_min = slope[good].min()
+    s_min = slope[good].min() if good.any() else np.inf
+    if reduce_min is not None:
+        # several strips: the smallest positive slope of the WHOLE grid
+        s_min = reduce_min(float(s_min))
+        if (nz + nn + ni) == 0 or not np.isfinite(s_min):
+            return slope
     if report is not None:
-        report.update(nz=nz, nn=nn, ni=ni, S_min=s_min, S_max=slope[good].max())
+        report.update(nz=nz, nn=nn, ni=ni, S_min=s_min,
+                      S_max=slope[good].max() if good.any() else s_min)
     slope[wz] = s_min
     slope[wn] = s_min
     slope[wi] = s_min
@@ -43,13 +49,15 @@ def channel_ds(sinu, ds):
 
 def setup_channels(strip, wave, law, dt, da, slope, width, angle, rough,
                    sinu=1.0, d0=0.0, outlets=(), allow_packed=True,
-                   ds=None, report=None):
+                   ds=None, report=None, reduce_min=None):
     """Upload parameters and the initial state; returns a dict of the host
     arrays the BMI component keeps (S_bed, ds, initial vol ...).
 
     slope, width, angle [rad], rough (nval or z0val), sinu, d0: 0-d or
     [ny, nx] float64, as they stand after read_input_files()
     (channels_base.py:2142-2200).  The D8 grid must already be on the strip.
+    reduce_min: with several strips, a callable returning the minimum of a
+    float over all strips (remove_bad_slopes needs the grid-wide value).
     """
     assert isinstance(strip, Strip)
     ny, nx = strip.ny, strip.nx
@@ -61,7 +69,7 @@ def setup_channels(strip, wave, law, dt, da, slope, width, angle, rough,
         slope = np.zeros((ny, nx), dtype='float64') + slope
     slope = np.float64(slope)
     if wave == L.KINEMATIC:
-        slope = remove_bad_slopes(slope, report)                # :949-950
+        slope = remove_bad_slopes(slope, report, reduce_min)    # :949-950
     d = np.zeros((ny, nx), dtype='float64')
     d += d0                                                     # :903
     tan_a, cos_a = np.tan(angle), np.cos(angle)
