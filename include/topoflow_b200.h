@@ -163,7 +163,7 @@ int tf_chan_init(tf_handle h, int wave, int law, double dt,
  * 'water-liquid__mass-per-volume_density', channels_base.py:165, :1577). */
 int tf_chan_set_rho(tf_handle h, double rho);
 
-/* Overwrite one materialised state grid (TF_F_VOL, TF_F_D, TF_F_U, TF_F_QNEXT)
+/* Overwrite one materialised state grid (TF_F_VOL, TF_F_D, TF_F_U, TF_F_Q, TF_F_QNEXT)
  * with host data: the initial state of initialize_computed_vars
  * (channels_base.py:900-960), or a restart. */
 int tf_chan_set_state(tf_handle h, int which, const double* grid);

@@ -331,8 +331,6 @@ class channels_component(BMI_base.BMI_component):
                         allow_packed=getattr(self, 'ALLOW_PACKED', True))
         strip.set_state(L.F_VOL, vol)
         strip.set_state(L.F_D, d)
-        if not self.KINEMATIC_WAVE:
-            strip.set_state(L.F_S_FREE, s_free0)
         # host views: d, vol, A_wet are known; the rest start at zero (:900-967)
         self._host.update(d=d, vol=vol, A_wet=A_wet, S_free=s_free0)
         self._host['P_wet'] = width + (np.float64(2) * d / cos_a)

@@ -61,7 +61,6 @@ extern "C" int tf_chan_init(tf_handle h, int wave, int law, double dt, const dou
     TF_TRY(raster_alloc(h, h->Qa, 0));
     TF_TRY(raster_alloc(h, h->Qb, 0));
     TF_TRY(raster_alloc(h, h->mstate, 0));
-    if (wave != TF_KINEMATIC) TF_TRY(raster_alloc(h, h->sfree, 0));
     if (wave == TF_DYNAMIC) TF_TRY(raster_alloc(h, h->u2, 0));
     h->Qcur = h->Qa.p; h->Qnext = h->Qb.p;
     TF_TRY(chan_layout_init(h, allow_packed));
@@ -85,6 +84,7 @@ extern "C" int tf_chan_init(tf_handle h, int wave, int law, double dt, const dou
     TF_CUDA(cudaMemcpy(h->bad, init_bad, sizeof(init_bad), cudaMemcpyHostToDevice));
     h->chan_ready = true;
     h->state_dirty = true;
+    h->steps_done = 0;
     h->acc_ms = 0.0; h->acc_steps = 0; h->acc_launches = 0; h->timing_open = false;
     TF_CUDA(cudaStreamSynchronize(h->stream));
     return 0;
@@ -101,9 +101,6 @@ extern "C" int tf_chan_set_state(tf_handle h, int which, const double* grid) {
         case TF_F_U: r = h->u; break;
         case TF_F_QNEXT: r.p = h->Qnext; break;
         case TF_F_Q: r.p = h->Qcur; break;
-        case TF_F_S_FREE:
-            TF_CHECK(h->sfree.p != nullptr, "tf_chan_set_state: S_free is not stored for the kinematic wave");
-            r = h->sfree; break;
         default:
             tf_set_error("tf_chan_set_state: field %d is not a stored state grid", which);
             return 1;

@@ -14,7 +14,7 @@ static inline ChanArgs chan_args(tf_handle h, int y_begin, int y_end) {
     a.dt = h->dt; a.rho = h->rho;
     a.Q = h->Qcur; a.Qn = h->Qnext;
     a.vol = h->vol.p; a.d = h->d.p; a.u = h->u.p; a.u_old = h->u2.p;
-    a.sfree = h->sfree.p;
+    a.steps_done = h->steps_done;
     a.Rgrid = h->R_is_grid ? h->R.p : nullptr;
     a.Rs = h->R_scalar;
     a.da_rows = h->da_rows + 1;

@@ -17,6 +17,9 @@
 #ifndef TF_MINBLOCKS
 #define TF_MINBLOCKS 6
 #endif
+#ifndef TF_MINBLOCKS_AB
+#define TF_MINBLOCKS_AB 5
+#endif
 
 struct ChanArgs {
     int nx, ny, pitch;
@@ -30,7 +33,7 @@ struct ChanArgs {
     double* d;
     double* u;                     // velocity written by this step
     const double* u_old;           // dynamic wave: last step's velocity
-    double* sfree;                 // diffusive / dynamic
+    long long steps_done;          // time steps taken since tf_chan_init
     const double* Rgrid;           // NULL -> Rs
     double Rs;
     const double* da_rows;         // [y], y = -1 .. ny
@@ -221,7 +224,7 @@ k_step_kinematic(const ChanArgs a) {
 // diffusive / dynamic wave, phase A: volume and depth of every cell
 // ---------------------------------------------------------------------------
 template <bool PACKED>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, TF_MINBLOCKS_AB)
 k_phase_a(const ChanArgs a) {
     const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
     const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;

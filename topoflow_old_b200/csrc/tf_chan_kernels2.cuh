@@ -24,13 +24,13 @@ __device__ __forceinline__ double free_slope(const ChanArgs& a, int64_t idx, int
 //   WAVE 2: channels_dynamic_wave.py:92-341
 // ---------------------------------------------------------------------------
 template <bool PACKED, int LAW, int WAVE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, TF_MINBLOCKS_AB)
 k_phase_b(const ChanArgs a) {
     const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
     const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
     if (x4 >= a.pitch || y >= a.y_end) return;
     const int64_t i = (int64_t)y * a.pitch + x4;
-    double d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT], S[CPT], n[CPT], u[CPT], Qn[CPT], sf[CPT];
+    double d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT], S[CPT], n[CPT], u[CPT], Qn[CPT];
     int code[CPT], ms[CPT];
     ld4c(a.d + i, d);
     ld4(a.code + i, code);
@@ -80,12 +80,10 @@ k_phase_b(const ChanArgs a) {
             uu = np_max0(M * vinv);                                // :318-331
         }
         if (noflow) uu = 0.0;                                      // channels_base.py:1783-1791
-        sf[k] = s_free;
         u[k] = uu;
         Qn[k] = uu * xs.A_wet;
         if (x4 + k < a.nx && bad_value(uu)) flag_bad(a, 1, x4 + k, y);
     }
-    st4(a.sfree + i, sf);
     st4(a.u + i, u);
     st4(a.Qn + i, Qn);
 }
@@ -215,7 +213,12 @@ k_derive(const ChanArgs a, int which, int wave, double* out) {
         case TF_F_FROUDE: r = (d > 0.0) ? a.u[i] / sqrt(TF_G * d) : 0.0; break;   // :1807
         case TF_F_WIDTH: r = w; break;
         case TF_F_MUTATED: r = (double)m; break;
-        case TF_F_S_FREE: r = (wave == 0) ? S : a.sfree[i]; break;
+        case TF_F_S_FREE: {
+            // not stored: S_bed + (d - d[parent]) / ds (:1542-1543), clipped at 0 by the
+            // diffusive wave (channels_diffusive_wave.py:118); S_bed before the first step (:889)
+            const double sf = free_slope(a, i, code, d, S, ds);
+            r = (wave == 0 || a.steps_done == 0) ? S : ((wave == 1) ? np_max0(sf) : sf);
+        } break;
         default: break;
     }
     out[i] = r;

@@ -131,6 +131,7 @@ static int queue_steps(tf_handle h, int n_steps, int record) {
         }
     }
     h->acc_steps += n_steps;
+    h->steps_done += n_steps;
     return 0;
 }
 
@@ -231,7 +232,7 @@ static double layout_bytes_per_cell(tf_handle h) {
             + 32 /*vol, d, u, Qnext w*/;
     } else {
         const double A = 8 + 8 + 3 + shape + 4 + R + 16;              // phase A
-        double B = 8 /*d*/ + 2 + shape + 4 + sr + 24;                 // phase B: sfree, u, Qn
+        double B = 8 /*d*/ + 2 + shape + 4 + sr + 16;                 // phase B: u, Qn
         if (h->wave == TF_DYNAMIC) B += 8 + 8 + 8 + 1;                // Q, vol, u_old, mask
         b = A + B;
     }
@@ -259,7 +260,7 @@ extern "C" int tf_chan_timing(tf_handle h, double* out4) {
 
 int chan_free(tf_handle h) {
     raster_free(h->vol); raster_free(h->d); raster_free(h->u); raster_free(h->u2);
-    raster_free(h->Qa); raster_free(h->Qb); raster_free(h->R); raster_free(h->sfree);
+    raster_free(h->Qa); raster_free(h->Qb); raster_free(h->R);
     raster_free(h->f); raster_free(h->mstate);
     raster_free(h->w64); raster_free(h->tan64); raster_free(h->cos64);
     raster_free(h->S64); raster_free(h->n64); raster_free(h->ds64);

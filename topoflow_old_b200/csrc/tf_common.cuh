@@ -129,11 +129,12 @@ struct tf_handle_s {
     int wave = 0, law = 0, packed = 0;
     int mut_width = 0, mut_angle = 0;
     double dt = 0.0, rho = 1000.0;
+    long long steps_done = 0;             // since tf_chan_init
     bool state_dirty = true;              // mstate must be rebuilt from d
     double* da_rows = nullptr;            // device [ny + 2] (index y + 1)
     bool chan_ready = false;
     // state
-    Raster<double> vol, d, u, u2, Qa, Qb, R, sfree, f;
+    Raster<double> vol, d, u, u2, Qa, Qb, R, f;
     double *Qcur = nullptr, *Qnext = nullptr;   // -> Qa.p / Qb.p
     double *ucur = nullptr, *unext = nullptr;   // dynamic wave double buffer
     bool R_is_grid = false;

@@ -86,6 +86,4 @@ def setup_channels(strip, wave, law, dt, da, slope, width, angle, rough,
     strip.set_state(L.F_VOL, vol)
     strip.set_state(L.F_D, d)
     # u = 0, so the first Q = u * A_wet is 0 everywhere (:900, :1188)
-    if wave != L.KINEMATIC:
-        strip.set_state(L.F_S_FREE, slope)                      # S_free = S_bed.copy(), :889
     return dict(S_bed=slope, ds=ds, vol0=vol, d0=d, A_wet0=A_wet)
