@@ -14,5 +14,11 @@ Parity status: PINNED.
                     (components/tests/test_d8_base_UNFINISHED.py:101-125)
   * routing       : reproduces the shipped Test_Plane_Canal hydrographs
                     (examples/Test_Plane_Canal/00_Output_Files/Case1_0D-*.txt)
+                    and, driven through a restatement of the EMELI loop
+                    (oracle/coupling.py), the shipped Treynor hydrographs of
+                    Test1_kin_wave and Test2_diff_wave digit for digit, with
+                    Q/u/d peaks equal to the console log to 12 digits;
+                    Test12_dynam_wave identical through the peak, within 1e-5
+                    on the recession (glibc vs the 2017 macOS libm)
 see tests/test_oracle_*.py.
 """
