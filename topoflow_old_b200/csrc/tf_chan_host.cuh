@@ -25,6 +25,7 @@ static inline ChanArgs chan_args(tf_handle h, int y_begin, int y_end) {
     a.S64 = h->S64.p; a.n64 = h->n64.p; a.ds64 = h->ds64.p;
     a.w32 = h->w32.p; a.S32 = h->S32.p; a.n32 = h->n32.p; a.ds32 = h->ds32.p;
     a.aidx = h->aidx.p; a.lut = h->lut;
+    a.kfac = h->kfac.p;
     a.bad = h->bad;
     return a;
 }

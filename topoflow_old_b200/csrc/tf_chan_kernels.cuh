@@ -49,6 +49,7 @@ struct ChanArgs {
     const float *w32, *S32, *n32, *ds32;
     const uint8_t* aidx;
     const double* lut;             // [256] tan, [256] cos
+    const double* kfac;            // kinematic + Manning: sqrt(S_bed) / n, float64
     long long* bad;                // [0] depth, [1] velocity: min bad global index
 };
 
@@ -176,7 +177,12 @@ __device__ __forceinline__ void store_mstate(const ChanArgs& a, int64_t i, const
 // ---------------------------------------------------------------------------
 // kinematic wave: the whole step in one pass
 // ---------------------------------------------------------------------------
-template <bool PACKED, int LAW>
+// KF: S_bed and n never change in the kinematic wave, so Manning's
+// (Rh^(2/3) * sqrt(S)) / n is evaluated as Rh^(2/3) * (sqrt(S)/n) with the
+// factor precomputed once on the host (one float64 read instead of two
+// float32 reads, a square root and a division per cell and step).  The
+// regrouping moves u by at most 1 ulp, next to the ~2 ulp of the cube root.
+template <bool PACKED, int LAW, bool KF>
 __global__ void __launch_bounds__(256, TF_MINBLOCKS)
 k_step_kinematic(const ChanArgs a) {
     const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
@@ -186,14 +192,16 @@ k_step_kinematic(const ChanArgs a) {
     double Q[CPT], v[CPT], d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT], S[CPT], n[CPT], u[CPT], Qn[CPT];
     int code[CPT], m[CPT], ms[CPT];
     volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
-    load_slope_rough<PACKED>(a, i, S, n);
+    if (KF) ld4(a.kfac + i, S);
+    else load_slope_rough<PACKED>(a, i, S, n);
     bool bad_d = false, bad_u = false;
     int bx = 0;
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
         const bool noflow = (code[k] == 0);
         const XSection xs = chan_xsection(d[k], w[k], t[k], c[k], noflow);
-        double uu = chan_velocity<LAW>(xs.Rh, S[k], n[k], d[k]);   // kinematic: S = S_bed
+        double uu = KF ? pow_two_thirds(xs.Rh) * S[k]
+                       : chan_velocity<LAW>(xs.Rh, S[k], n[k], d[k]);   // kinematic: S = S_bed
         if (noflow) uu = 0.0;                                      // :1783-1791
         u[k] = uu;
         Qn[k] = uu * xs.A_wet;                                     // :1188 of the next step

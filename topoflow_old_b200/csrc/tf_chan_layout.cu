@@ -10,6 +10,9 @@
 // channels_base.py:2150-2153) and the grid must hold at most 255 distinct
 // bank angles.  Arithmetic is float64 in both layouts; only the bytes read
 // per cell differ.
+#include <math.h>
+#include <stdlib.h>
+
 #include <map>
 #include <utility>
 
@@ -118,6 +121,14 @@ int chan_layout_init(tf_handle h, int allow_packed) {
                 if (y < 0 || y >= g.ny || x >= g.nx) row[x] = 3.0e38f;
         }
         TF_CUDA(cudaMemcpy(h->dw.base, dw.data(), sizeof(float) * (size_t)g.n_alloc, cudaMemcpyHostToDevice));
+    }
+    // kinematic + Manning: conveyance factor sqrt(S_bed)/n, once, on the host
+    raster_free(h->kfac);
+    if (h->wave == TF_KINEMATIC && h->law == TF_MANNING && !getenv("TF_B200_NO_KFAC")) {
+        HostParam K;
+        K.grid.resize(n);
+        for (size_t i = 0; i < n; ++i) K.grid[i] = sqrt(hp_at(S, i)) / hp_at(N, i);
+        TF_TRY(fill_raster<double>(h, h->kfac, K, 1.0));
     }
     // free the host copies: the device rasters are the parameters from here on
     for (int k = 0; k < TF_P_COUNT; ++k) {

@@ -5,7 +5,12 @@
 // one launch covering rows [y0, y1)
 static int launch_kinematic(tf_handle h, cudaStream_t s, int y0, int y1) {
     ChanArgs a = chan_args(h, y0, y1);
-    TF_DISPATCH(h, (k_step_kinematic<P, L><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a)));
+    if (h->kfac.p) {
+        if (h->packed) k_step_kinematic<true, 0, true><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a);
+        else k_step_kinematic<false, 0, true><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a);
+    } else {
+        TF_DISPATCH(h, (k_step_kinematic<P, L, false><<<tile_grid(h->g, y1 - y0), dim3(32, 8), 0, s>>>(a)));
+    }
     TF_LAUNCHED(h, s, "k_step_kinematic");
     h->acc_launches++;
     return 0;
@@ -228,8 +233,8 @@ static double layout_bytes_per_cell(tf_handle h) {
     const double sr = h->packed ? 8 : 16;                            // S, roughness
     const double R = h->R_is_grid ? 8 : 0;
     if (h->wave == TF_KINEMATIC) {
-        b = 8 /*Q*/ + 8 /*vol r*/ + 1 + 1 + 1 /*code, mask, mstate*/ + shape + 4 /*dw*/ + sr + R
-            + 32 /*vol, d, u, Qnext w*/;
+        b = 8 /*Q*/ + 8 /*vol r*/ + 1 + 1 + 1 /*code, mask, mstate*/ + shape + 4 /*dw*/
+            + (h->kfac.p ? 8 : sr) + R + 32 /*vol, d, u, Qnext w*/;
     } else {
         const double A = 8 + 8 + 3 + shape + 4 + R + 16;              // phase A
         double B = 8 /*d*/ + 2 + shape + 4 + sr + 16;                 // phase B: u, Qn
@@ -263,7 +268,7 @@ int chan_free(tf_handle h) {
     raster_free(h->Qa); raster_free(h->Qb); raster_free(h->R);
     raster_free(h->f); raster_free(h->mstate);
     raster_free(h->w64); raster_free(h->tan64); raster_free(h->cos64);
-    raster_free(h->S64); raster_free(h->n64); raster_free(h->ds64);
+    raster_free(h->S64); raster_free(h->n64); raster_free(h->ds64); raster_free(h->kfac);
     raster_free(h->w32); raster_free(h->S32); raster_free(h->n32); raster_free(h->ds32);
     raster_free(h->aidx);
     void* ptrs[] = {h->lut, h->ds_rows, h->da_rows, h->outlet_idx, h->taps, h->canal_taps,

@@ -142,6 +142,7 @@ struct tf_handle_s {
     Raster<uint8_t> mstate;               // bit0 mutated, bit1 pending
     // parameters, generic layout (float64)
     Raster<double> w64, tan64, cos64, S64, n64, ds64;
+    Raster<double> kfac;                  // sqrt(S_bed)/n for the kinematic Manning step
     // parameters, packed layout (float32 + angle table)
     Raster<float> w32, S32, n32, ds32;
     Raster<uint8_t> aidx;
