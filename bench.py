@@ -23,6 +23,7 @@ import time
 
 import numpy as np
 
+_OUT = sys.stdout
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -48,14 +49,14 @@ def peaks():
 # ---------------------------------------------------------------------------
 # inputs
 # ---------------------------------------------------------------------------
-def synth_inputs(nx, global_ny, row0, nrows, seed=20170226):
+def synth_inputs(nx, global_ny, row0, nrows, seed=20170226, n_procs=1):
     """DEM strip (+ its halo rows) and the float32 parameter grids, as the
     reference would read them from RTG files."""
     from concurrent.futures import ThreadPoolExecutor
     from topoflow_old_b200.utils import synth
     lo, hi = max(row0 - 1, 0), min(row0 + nrows + 1, global_ny)
     chunks = [(a, min(a + 512, hi)) for a in range(lo, hi, 512)]
-    with ThreadPoolExecutor(max_workers=min(32, os.cpu_count() or 1)) as ex:
+    with ThreadPoolExecutor(max_workers=max(2, min(32, (os.cpu_count() or 1) // n_procs))) as ex:
         parts = list(ex.map(lambda ab: synth.fractal_dem(nx, global_ny, row0=ab[0], nrows=ab[1] - ab[0],
                                                          seed=seed, cell=CELL, roughness=8.0), chunks))
     dem = np.concatenate(parts, axis=0)
@@ -79,7 +80,7 @@ def build_strip(args, rank, nranks, device, unique_id=None, reduce_min=None):
     nx, global_ny = args.size, args.size * nranks          # weak scaling: size^2 cells per GPU
     row0, ny = strips.strip_rows(global_ny, nranks, rank)
     t0 = time.time()
-    dem, north, south, nval, width, angle = synth_inputs(nx, global_ny, row0, ny)
+    dem, north, south, nval, width, angle = synth_inputs(nx, global_ny, row0, ny, n_procs=nranks)
     log('[rank %d] synthetic inputs %.1fs' % (rank, time.time() - t0))
     s = Strip(nx, ny, device=device)
     if nranks > 1:
@@ -260,6 +261,10 @@ def run_gpu(args):
         uid = D.bcast_bytes(uid)
     s = build_strip(args, D.rank, D.world, D.local_rank, uid,
                     reduce_min=(lambda v: -D.max(-v)) if D.world > 1 else None)
+    # torch creates its own communicator lazily at the first collective: do that (and let every
+    # rank finish its set-up) well before the timed region, or the skew lands inside it
+    D.barrier()
+    D.max(0.0)
     cells = float(args.size) * args.size              # per GPU
     K, W = args.steps, max(args.warmup, 0)
 
@@ -267,6 +272,7 @@ def run_gpu(args):
     s.step_async(W)
     s.sync()
     s.timing()
+    D.barrier()
     D.barrier()
     sampler = ClockSampler(D.local_rank)
     sampler.start()
@@ -338,7 +344,7 @@ def run_gpu(args):
     s.close()
     D.close()
     if line is not None:
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_OUT, flush=True)
 
 
 def _have_py27():
@@ -371,10 +377,21 @@ def run_reference(args):
                                        'found' if _have_py27() else 'unavailable on this box')},
         'e2e': {'value': v, 'unit': 'cell-updates/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_OUT, flush=True)
+
+
+def _claim_stdout():
+    """Point fd 1 at stderr for the whole run (NCCL and friends print banners to
+    stdout) and return a file on the real stdout for the one JSON line."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), 'w')
+    os.dup2(2, 1)
+    return real
 
 
 def main():
+    global _OUT
+    _OUT = _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=20)

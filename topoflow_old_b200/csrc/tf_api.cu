@@ -142,8 +142,9 @@ extern "C" int tf_set_strip(tf_handle h, int row_offset, int global_ny,
     TF_CHECK(row_offset >= 0 && row_offset + h->g.ny <= global_ny,
              "tf_set_strip: rows [%d, %d) outside a grid of %d rows",
              row_offset, row_offset + h->g.ny, global_ny);
-    TF_CHECK((int64_t)h->g.nx * global_ny < ((int64_t)1 << 31),
-             "tf_set_strip: global grid does not fit int32 cell IDs");
+    // A global grid of >= 2^31 cells cannot carry the reference's int32 calendar
+    // IDs (d8_base.py:675); routing does not need them, so only the parent-ID
+    // product becomes unavailable (tf_d8_get refuses it).
     h->g.row_offset = row_offset;
     h->g.global_ny = global_ny;
     h->g.has_north = has_north != 0;

@@ -200,12 +200,12 @@ k_finalize(D8Args a, const int16_t* __restrict__ raw, const uint8_t* __restrict_
     // update_parent_ID_grid, d8_global.py:574-644 (int32 calendar IDs)
     const int gy = y + a.row_offset;
     const int nx = a.nx;
-    const int n_pixels = nx * a.global_ny;
-    int pid = 0;
+    const long long n_pixels = (long long)nx * a.global_ny;
+    long long pid = 0;
     if (c > 0) {
         const int k = __ffs(c) - 1;
         const int incs[8] = {-nx + 1, 1, nx + 1, nx, nx - 1, -1, -nx - 1, -nx};
-        pid = gy * nx + x + incs[k];
+        pid = (long long)gy * nx + x + incs[k];
         if (x == nx - 1) {
             if (a.lr_periodic) { if (c == 1 || c == 2 || c == 4) pid -= nx; }
             else pid = 0;
@@ -223,7 +223,7 @@ k_finalize(D8Args a, const int16_t* __restrict__ raw, const uint8_t* __restrict_
             else pid = 0;
         }
     }
-    parent[i] = pid;
+    parent[i] = (int32_t)pid;      // exact while the global grid has < 2^31 cells
     // update_flow_width_grid :863-935, update_flow_length_grid :949-1004
     const float rx = dx[y], ry = dy[y], rd = dd[y];
     dw[i] = len_by_code(c, rd, ry, rx, rx);
@@ -567,7 +567,11 @@ extern "C" int tf_d8_get(tf_handle h, int which, void* host_out) {
     TF_CHECK(h->have_d8, "tf_d8_get: no D8 grid yet");
     switch (which) {
         case TF_D8_CODE: return raster_download<uint8_t>(h, h->code.p, (uint8_t*)host_out);
-        case TF_D8_PARENT_ID: return raster_download<int32_t>(h, h->parent.p, (int32_t*)host_out);
+        case TF_D8_PARENT_ID:
+            TF_CHECK((int64_t)h->g.nx * h->g.global_ny < ((int64_t)1 << 31),
+                     "tf_d8_get: the global grid has >= 2^31 cells; the reference's int32 parent IDs "
+                     "(d8_base.py:675) cannot represent it");
+            return raster_download<int32_t>(h, h->parent.p, (int32_t*)host_out);
         case TF_D8_DS: return raster_download<float>(h, h->ds0.p, (float*)host_out);
         case TF_D8_DW: return raster_download<float>(h, h->dw.p, (float*)host_out);
         case TF_D8_AREA:
