@@ -12,9 +12,11 @@ Parity status: PINNED.
   * D8 area       : bit-exact (float32) vs Treynor_area.rtg
   * tie-break LUT : equals the RT3 16x16 table, sum 10161
                     (components/tests/test_d8_base_UNFINISHED.py:101-125)
-  * routing       : reproduces the shipped Test_Plane_Canal hydrographs
-                    (examples/Test_Plane_Canal/00_Output_Files/Case1_0D-*.txt)
-                    and, driven through a restatement of the EMELI loop
+  * routing       : reproduces the shipped Test_Plane_Canal run in full -- rain
+                    grid + the 240 s canal, replayed through oracle/coupling.py:
+                    every column of Case1_0D-{Q,d,u}.txt digit for digit and
+                    all 60 frames of Case1_2D-Q.rts bit for bit (this pins
+                    update_diversions, channels_base.py:1226-1297) -- and, driven through a restatement of the EMELI loop
                     (oracle/coupling.py), the shipped Treynor hydrographs of
                     Test1_kin_wave and Test2_diff_wave digit for digit, with
                     Q/u/d peaks equal to the console log to 12 digits;

@@ -13,6 +13,7 @@ Follows, including their aliasing quirks:
   components/met_base.py:650-700, :1013-1038, :1787-1810 (P series, P_rain)
   components/infil_base.py:216-264, :500-513, :592-647, :700-728, :784-823
   components/infil_green_ampt.py:336-389, Green_Ampt_Infil_Rate_v1
+  components/diversions_fraction_method.py:230-252, :418-546, :622-734 (canals)
 """
 import numpy as np
 
@@ -116,6 +117,52 @@ class MetSeries(Component):
         self.P_rain[()] = self.P * (self.T_air > 0)             # :1037-1038, in place
         if self.time_index > 0:
             self.read_input_files()
+        self.advance()
+
+
+class MetGrid(Component):
+    """Rain from one grid [m/s] that never changes (P_type = Grid)."""
+    provides = ('P_rain', 'rho_H2O')
+
+    def __init__(self, dt, P, rho_H2O=1000.0):
+        Component.__init__(self, dt)
+        self.P = P
+        self.P_rain = np.zeros_like(P)
+        self.rho_H2O = scalar(rho_H2O)
+
+    def update(self):
+        self.P_rain[:] = self.P                                 # T_air > 0
+        self.advance()
+
+
+class CanalDiversions(Component):
+    """diversions_fraction_method with canals only: what enters a canal leaves
+    it nt = ceil(travel_time / dt) updates later.  canals_in_Q comes from the
+    channels component; canals_out_Q is updated in place (:701-704)."""
+    provides = ('n_canals', 'canals_Q_fraction', 'canals_in_x', 'canals_in_y',
+                'canals_out_x', 'canals_out_y', 'canals_out_Q')
+    uses = (('canals_in_Q', 'chan', 'canals_in_Q'),)
+
+    def __init__(self, dt, dx, dy, in_cols, in_rows, out_cols, out_rows, fractions, travel_times):
+        Component.__init__(self, dt)
+        n = len(in_cols)
+        self.n_canals = np.array(n, dtype='int32')
+        self.canals_Q_fraction = np.array(fractions, dtype='float64')
+        self.nt_canals = np.ceil(np.array(travel_times, dtype='float64') / self.dt)   # :509
+        self.canals_in_x = np.int32(in_cols) * dx                # :519-522
+        self.canals_in_y = np.int32(in_rows) * dy
+        self.canals_out_x = np.int32(out_cols) * dx
+        self.canals_out_y = np.int32(out_rows) * dy
+        self.canal_Q = np.zeros([n, int(self.nt_canals.max())], dtype='float64')      # :533
+        self.canals_out_Q = np.zeros([n], dtype='float64')
+        self.canals_in_Q = np.zeros([n], dtype='float64')
+
+    def update(self):                                           # :622-734
+        self.canal_Q[:, 0] = self.canals_in_Q
+        self.canals_out_Q[:] = np.zeros(int(self.n_canals), dtype='float32')
+        for k in range(int(self.n_canals)):
+            self.canals_out_Q[k] = self.canal_Q[k, int(self.nt_canals[k]) - 1]
+        self.canal_Q = np.roll(self.canal_Q, 1, axis=1)
         self.advance()
 
 

@@ -99,3 +99,111 @@ def run(golden_dir, channels, minutes):
     while float(channels.time) < minutes * 60 + 4:
         fw.sweep()
     return fw
+
+
+# ---- Test_Plane_Canal/Case1: constant rain grid + one canal, everything else Disabled ----
+PLANE_PTS = [(10, 18), (1, 18), (10, 16), (1, 16), (10, 3), (9, 3), (8, 3), (1, 3),
+             (3, 5), (2, 5), (1, 5), (1, 1)]                     # Case1_outlets.txt as (row, col)
+PLANE_DIV_LONG = {'n_canals': 'canals__count',
+                  'canals_Q_fraction': 'canals_entrance_water__volume_fraction',
+                  'canals_in_x': 'canals_entrance__x_coordinate',
+                  'canals_in_y': 'canals_entrance__y_coordinate',
+                  'canals_out_x': 'canals_exit__x_coordinate',
+                  'canals_out_y': 'canals_exit__y_coordinate',
+                  'canals_out_Q': 'canals_exit_water__volume_flow_rate'}
+
+
+def plane_grid(golden_dir, name):
+    p = os.path.join(golden_dir, 'plane_canal', name)
+    return np.fromfile(p, dtype='<f4').reshape(20, 20)
+
+
+def plane_rain(golden_dir):
+    # met_base.py:1799-1800 -> model_input.read_next(..., factor=mmph_to_mps): float32 data
+    # scaled in place (float32 arithmetic under NumPy-1 casting), then widened
+    rain = plane_grid(golden_dir, 'Rain_100mmph_on_right.rtg')
+    return np.float64(rain * np.float32(np.float64(1) / np.float64(3600000)))
+
+
+def plane_diversions(golden_dir):
+    """plane_canals.txt through read_canal_data (diversions_fraction_method.py:418-546)."""
+    kv = {}
+    for line in open(os.path.join(golden_dir, 'plane_canal', 'plane_canals.txt')):
+        if ':' in line:
+            k, v = line.split(':', 1)
+            kv[k.strip()] = float(v.split()[0])
+    assert kv['n_canals'] == 1
+    return cp.CanalDiversions(6.0, 10.0, 10.0, [int(kv['canal_in_col'])], [int(kv['canal_in_row'])],
+                              [int(kv['canal_out_col'])], [int(kv['canal_out_row'])],
+                              [kv['Q_fraction']], [kv['travel_time']])
+
+
+class OraclePlaneChannels(cp.Component):
+    provides = ('Q_outlet', 'canals_in_Q')
+    uses = (('P_rain', 'met', 'P_rain'), ('canals_out_Q', 'div', 'canals_out_Q'))
+
+    def __init__(self, golden_dir, div):
+        dem, slope = plane_grid(golden_dir, 'plane_DEM.rtg'), plane_grid(golden_dir, 'plane_slope.rtg')
+        b = od8.build(dem, 10.0, 10.0)
+        ch = och.ChannelsOracle(b, och.KINEMATIC, dt=6.0, da=np.float64(10.0) * np.float64(10.0),
+                                slope=np.float64(slope), width=10.0, angle=0.0, nval=0.3,
+                                outlet_ID=PLANE_PTS[0])
+        self.ch, self.dt, self.time = ch, ch.dt, ch.time
+        self.time_index, self.status = 0, 'initialized'
+        self.Q_outlet = ch.Q_outlet
+        ids = lambda x, y: (np.int32(y / 10.0), np.int32(x / 10.0))     # channels_base.py:1030-1036
+        ch.set_canals(*(ids(div.canals_in_x, div.canals_in_y) + ids(div.canals_out_x, div.canals_out_y)
+                        + (div.canals_Q_fraction, div.canals_out_Q)))
+        self.canals_in_Q = ch.canals_in_Q = np.zeros(1, dtype='float64')
+        self.rows = {v: [] for v in 'Qdu'}
+
+    def update(self):
+        ch = self.ch
+        ch.P_rain, ch.canals_out_Q = self.P_rain, self.canals_out_Q
+        t = float(ch.time)
+        ch.update()
+        self.time, self.canals_in_Q = ch.time, ch.canals_in_Q
+        if int(t) % 30 == 0:                                   # channels_base.py:2481-2491
+            for v in 'Qdu':                                    # text_ts_files.py:149-186
+                vals = np.float32(getattr(ch, v)[tuple(np.array(PLANE_PTS).T)])
+                self.rows[v].append([float('%15.7f' % (t / 60.0))] + [float('%15.7f' % x) for x in vals])
+        self.time_index += 1
+        self.status = 'updated'
+
+
+class BmiPlaneChannels(cp.Component):
+    """The CUDA component in the same seat: the diversions outputs are set into
+    it BEFORE initialize(), as emeli.initialize_comp_set does (emeli.py:1797-1828)."""
+    provides = ('Q_outlet', 'canals_in_Q')
+    uses = (('P_rain', 'met', 'P_rain'), ('canals_out_Q', 'div', 'canals_out_Q'))
+
+    def __init__(self, comp, cfg_file, div):
+        for attr, long_name in PLANE_DIV_LONG.items():
+            comp.set_values(long_name, getattr(div, attr))
+        for long_name in ('sinks__count', 'sources__count'):
+            comp.set_values(long_name, np.array(0, dtype='int32'))
+        comp.initialize(cfg_file=cfg_file, SILENT=True)
+        self.comp, self.dt, self.time = comp, comp.dt, comp.time
+        self.time_index, self.status = 0, 'initialized'
+        self.Q_outlet = comp.get_values('basin_outlet_water_x-section__volume_flow_rate')
+        self.canals_in_Q = comp.get_values('canals_entrance_water__volume_flow_rate')
+
+    def update(self):
+        c = self.comp
+        c.set_values('atmosphere_water__rainfall_volume_flux', self.P_rain)
+        c.set_values('canals_exit_water__volume_flow_rate', self.canals_out_Q)
+        c.update(-1.0)
+        self.time = c.time
+        self.canals_in_Q = c.get_values('canals_entrance_water__volume_flow_rate')
+        self.time_index += 1
+        self.status = c.get_status()
+
+
+def run_plane(golden_dir, make_channels, seconds=3600):
+    div = plane_diversions(golden_dir)
+    chan = make_channels(div)
+    met = cp.MetGrid(6000.0, plane_rain(golden_dir))
+    fw = cp.Framework(dict(met=met, div=div, chan=chan), ['met', 'div', 'chan'])   # Case1_providers.txt
+    while float(chan.time) < seconds:
+        fw.sweep()
+    return fw, chan

@@ -89,6 +89,34 @@ def test_plane_case_reproduces_the_reference_output_files(golden_dir, tmp_path):
     assert os.path.exists(os.path.join(d, 'Case1_2D-Q.rti')) and os.path.exists(os.path.join(d, 'Case1_2D-Q.bov'))
 
 
+def test_plane_canal_run_through_the_component(golden_dir, tmp_path):
+    """The shipped Case1 run as it was made: the CUDA component in the channels
+    seat of the replayed EMELI loop, with the canal.  All columns of the three
+    text files and every frame of the Q stack."""
+    from tests import replay
+    from topoflow_old_b200.components import channels_kinematic_wave
+    d = stage(golden_dir, 'plane_canal', tmp_path)
+    comp = channels_kinematic_wave.channels_component()
+    cfg = os.path.join(d, 'Case1_channels_kinematic_wave.cfg')
+    fw, chan = replay.run_plane(golden_dir, lambda div: replay.BmiPlaneChannels(comp, cfg, div))
+    assert int(comp.n_canals) == 1 and comp.canal_in_IDs[0][0] == 10 and comp.canal_in_IDs[1][0] == 16
+    assert comp.canal_out_IDs[1][0] == 3
+    comp.finalize()
+    for var in 'Qdu':
+        mine = open(os.path.join(d, 'Case1_0D-%s.txt' % var)).read().splitlines()
+        gold = open(os.path.join(d, 'out', 'Case1_0D-%s.txt' % var)).read().splitlines()
+        a = np.array([r.split() for r in mine[2:122]], dtype=float)
+        b = np.array([r.split() for r in gold[2:]], dtype=float)
+        assert a.shape == b.shape == (120, 13)
+        assert np.max(np.abs(a - b)) <= 1.0000001e-7, var      # one unit of the 7th printed decimal
+        assert np.mean(a == b) > 0.999
+    mine = np.fromfile(os.path.join(d, 'Case1_2D-Q.rts'), dtype='<f4')[:60 * 400].reshape(60, 20, 20)
+    gold = np.fromfile(os.path.join(d, 'out', 'Case1_2D-Q.rts'), dtype='<f4').reshape(60, 20, 20)
+    ulp = np.abs(mine.view(np.int32).astype(np.int64) - gold.view(np.int32).astype(np.int64))
+    assert ulp.max() <= 1 and np.mean(ulp == 0) > 0.999         # fp64 within 1e-10 -> float32 rounding ties
+    assert gold[:, 10, 3].max() > 0.02 and mine[:, 10, 16].max() == 0.0
+
+
 @pytest.mark.parametrize('wave', ['kinematic', 'diffusive', 'dynamic'])
 def test_treynor_component_matches_oracle(golden_dir, tmp_path, wave):
     import importlib
