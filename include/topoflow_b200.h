@@ -20,6 +20,7 @@
 #ifndef TOPOFLOW_B200_H
 #define TOPOFLOW_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -205,6 +206,24 @@ int tf_chan_get(tf_handle h, int which, double* host_out);
 /* Interior min/max of Q, u, d: out[6] = Qmin,Qmax,umin,umax,dmin,dmax
  * (update_mins_and_maxes, channels_base.py:1890-1916). */
 int tf_chan_minmax(tf_handle h, double* out6);
+
+/* ---- output frames ---------------------------------------------------------
+ * Replaces the grid branch of write_output_files (channels_base.py:2465-2535)
+ * -> model_output.add_grid -> rts_file.add_grid (utils/rts_files.py:313-396):
+ * "grid = np.float32(grid); if SWAP_ENDIAN: grid.byteswap(True); tofile".
+ * The field (enum tf_field) is rounded to float32 (round to nearest even, as
+ * np.float32 does) and, when swap_endian != 0, byte-swapped ON THE DEVICE into
+ * a dense [ny, nx] frame, which is copied to host_out on a separate copy
+ * stream.  async != 0 returns at once: later tf_chan_step* calls overlap the
+ * copy, and host_out (best allocated with tf_host_alloc) is valid after
+ * tf_chan_frame_wait().  One frame may be in flight per handle; a second call
+ * waits on the device for the first copy to leave the frame buffer. */
+int tf_chan_frame(tf_handle h, int which, int swap_endian, float* host_out, int async);
+int tf_chan_frame_wait(tf_handle h);
+
+/* Page-locked host memory for frames and forcing grids (cudaHostAlloc). */
+int tf_host_alloc(size_t bytes, void** out);
+int tf_host_free(void* p);
 
 /* Device-side timing of everything queued by tf_chan_step* since the last
  * call: out[0] = elapsed ms (CUDA events on the handle's stream), out[1] =

@@ -259,3 +259,34 @@ def test_bad_values_are_flagged_like_check_flow():
         compare(s, ch, 'negative slope, diffusive')
     finally:
         s.close()
+
+
+def test_output_frames_are_the_float32_grids_the_reference_writes():
+    """tf_chan_frame: np.float32(grid) (+ byteswap) done on the device, the copy
+    overlapping later steps (rts_files.py:313-396)."""
+    from topoflow_old_b200 import _lib as L
+    c = make_case(157, 83, seed=31)                  # ragged: nx not a multiple of 32
+    s = gpu_for(c, 1, 2.0)
+    try:
+        s.set_R(float(c['P_rain']))
+        s.step(40)
+        for fid in (L.F_Q, L.F_D, L.F_U, L.F_F, L.F_RH):
+            want = np.float32(s.get(fid))
+            got = s.frame(fid)
+            assert got.dtype == np.float32 and got.shape == (83, 157)
+            assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), fid
+            swapped = s.frame(fid, swap_endian=True)
+            assert np.array_equal(swapped.view(np.uint32), want.byteswap().view(np.uint32)), fid
+        assert np.float32(s.get(L.F_Q)).max() > 0
+        # asynchronous: the frame is the state at the call, whatever runs afterwards
+        buf_q, buf_d = s.pinned_frame(), s.pinned_frame()
+        want_q, want_d = np.float32(s.get(L.F_Q)), np.float32(s.get(L.F_D))
+        s.frame(L.F_Q, out=buf_q, wait=False)
+        s.frame(L.F_D, swap_endian=True, out=buf_d, wait=False)   # waits on the device for the first copy
+        s.step(7)
+        s.frame_wait()
+        assert np.array_equal(buf_q.view(np.uint32), want_q.view(np.uint32))
+        assert np.array_equal(buf_d.view(np.uint32), want_d.byteswap().view(np.uint32))
+        assert not np.array_equal(np.float32(s.get(L.F_Q)), want_q)   # the state did move on
+    finally:
+        s.close()

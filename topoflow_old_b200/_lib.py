@@ -53,6 +53,10 @@ SIGNATURES = {
     'tf_chan_get': (C.c_int, [handle_t, C.c_int, _dp]),
     'tf_chan_minmax': (C.c_int, [handle_t, _dp]),
     'tf_chan_timing': (C.c_int, [handle_t, _dp]),
+    'tf_chan_frame': (C.c_int, [handle_t, C.c_int, C.c_int, _fp, C.c_int]),
+    'tf_chan_frame_wait': (C.c_int, [handle_t]),
+    'tf_host_alloc': (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
+    'tf_host_free': (C.c_int, [C.c_void_p]),
     'tf_sum_R_noalloc': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_void_p, C.c_double,
                                    C.c_double, C.c_void_p, C.c_void_p]),
     'tf_comm_unique_id': (C.c_int, [_u8p]),

@@ -553,16 +553,46 @@ class channels_component(BMI_base.BMI_component):
             self.save_pixel_values()
 
     def close_output_files(self):                              # :2503-2513
+        self.flush_frames()
+        self.__dict__.pop('_frame_bufs', None)                 # pinned memory goes with the strip
         for v, _, _ in self._OUT:
             if getattr(self, 'SAVE_%s_GRIDS' % v.upper(), False):
                 model_output.close_gs_file(self, v)
             if getattr(self, 'SAVE_%s_PIXELS' % v.upper(), False):
                 model_output.close_ts_file(self, v)
 
+    _FRAME_FIELD = {'Q': L.F_Q, 'u': L.F_U, 'd': L.F_D, 'f': L.F_F}
+
     def save_grids(self):                                      # :2517-2535
+        """rts_file.add_grid's float32 cast and byte swap happen on the device
+        (tf_chan_frame); the frame comes back on a copy stream into page-locked
+        memory while the next steps run, and is appended to the stack at the
+        next save (or at close).  The files end up byte-identical."""
+        self.flush_frames()
+        strip = self.d8.strip
+        pend = self.__dict__.setdefault('_frames', [])
+        bufs = self.__dict__.setdefault('_frame_bufs', {})
         for v, _, _ in self._OUT:
-            if getattr(self, 'SAVE_%s_GRIDS' % v.upper()):
+            if not getattr(self, 'SAVE_%s_GRIDS' % v.upper()):
+                continue
+            unit = getattr(self, v + '_rts_unit', None)
+            if unit is None:
+                continue
+            if np.dtype(unit.dtype) != np.float32:
                 model_output.add_grid(self, getattr(self, v), v, self.time_min)
+                continue
+            if v not in bufs:
+                bufs[v] = strip.pinned_frame()
+            strip.frame(self._FRAME_FIELD[v], unit.info.SWAP_ENDIAN, out=bufs[v], wait=False)
+            pend.append((unit, bufs[v]))
+
+    def flush_frames(self):
+        pend = self.__dict__.get('_frames')
+        if pend:
+            self.d8.strip.frame_wait()
+            for unit, buf in pend:
+                unit.add_frame(buf)
+            del pend[:]
 
     def save_pixel_values(self):                               # :2539-2557
         """The monitored cells are exactly the outlet taps the step returned,

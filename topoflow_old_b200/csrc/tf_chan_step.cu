@@ -168,18 +168,18 @@ extern "C" int tf_chan_step(tf_handle h, int n_steps, double* taps_out, double* 
     return 0;
 }
 
-extern "C" int tf_chan_get(tf_handle h, int which, double* host_out) {
-    TF_TRY(use_device(h));
+// Device pointer (cell (0,0), pitched) of a field: the state rasters as they
+// stand, anything else derived into the scratch raster first.
+int chan_derive_to_scratch(tf_handle h, int which, const double** src_out) {
     TF_CHECK(h->chan_ready, "tf_chan_get: call tf_chan_init first");
-    TF_CHECK(host_out != nullptr, "tf_chan_get: host_out is NULL");
     TF_CHECK(which >= 0 && which < TF_F_COUNT, "tf_chan_get: unknown field %d", which);
     const Geom& g = h->g;
     switch (which) {
-        case TF_F_VOL: return raster_download<double>(h, h->vol.p, host_out);
-        case TF_F_D: return raster_download<double>(h, h->d.p, host_out);
-        case TF_F_U: return raster_download<double>(h, h->u.p, host_out);
-        case TF_F_Q: return raster_download<double>(h, h->Qcur, host_out);
-        case TF_F_QNEXT: return raster_download<double>(h, h->Qnext, host_out);
+        case TF_F_VOL: *src_out = h->vol.p; return 0;
+        case TF_F_D: *src_out = h->d.p; return 0;
+        case TF_F_U: *src_out = h->u.p; return 0;
+        case TF_F_Q: *src_out = h->Qcur; return 0;
+        case TF_F_QNEXT: *src_out = h->Qnext; return 0;
         default: break;
     }
     TF_CHECK(!(which == TF_F_S_FREE && h->wave == TF_KINEMATIC),
@@ -194,7 +194,16 @@ extern "C" int tf_chan_get(tf_handle h, int which, double* host_out) {
     dim3 blk(64, 4), grd((g.nx + 63) / 64, (g.ny + 3) / 4);
     TF_DISPATCH(h, (k_derive<P, L><<<grd, blk, 0, h->stream>>>(a, which, h->wave, out)));
     TF_CUDA(cudaGetLastError());
-    return raster_download<double>(h, out, host_out);
+    *src_out = out;
+    return 0;
+}
+
+extern "C" int tf_chan_get(tf_handle h, int which, double* host_out) {
+    TF_TRY(use_device(h));
+    TF_CHECK(host_out != nullptr, "tf_chan_get: host_out is NULL");
+    const double* src = nullptr;
+    TF_TRY(chan_derive_to_scratch(h, which, &src));
+    return raster_download<double>(h, src, host_out);
 }
 
 extern "C" int tf_chan_minmax(tf_handle h, double* out6) {

@@ -162,6 +162,11 @@ struct tf_handle_s {
     double* partial = nullptr;            // device scratch for reductions
     int partial_cap = 0;
     double* scratch64 = nullptr;          // one raster for derived fields
+    // output frames (tf_output.cu)
+    float* frame32 = nullptr;             // device [ny*nx] dense float32 frame
+    cudaStream_t stream_io = nullptr;     // D2H copies of frames
+    cudaEvent_t ev_frame_ready = nullptr, ev_frame_done = nullptr;
+    bool frame_pending = false;
     // timing
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     bool timing_open = false;
@@ -185,6 +190,8 @@ int use_device(tf_handle h);
 int d8_free(tf_handle h);
 int chan_free(tf_handle h);
 int comm_free(tf_handle h);
+int output_free(tf_handle h);
+int chan_derive_to_scratch(tf_handle h, int which, const double** src_out);
 int comm_exchange_rows(tf_handle h, cudaStream_t s, void* const* arrays,
                        const size_t* elem_sizes, int n_arrays);
 int comm_allreduce_u64(tf_handle h, cudaStream_t s, unsigned long long* dev, int n);

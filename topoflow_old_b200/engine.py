@@ -33,12 +33,16 @@ class Strip(object):
         L.check(L.lib.tf_create(self.nx, self.ny, int(device), 0, C.byref(self._h)))
         self.n_outlets = 0
         self.n_canals = 0
+        self._pinned = []
 
     # -- lifetime ---------------------------------------------------------
     def close(self):
         if getattr(self, '_h', None) is not None and self._h.value:
-            L.lib.tf_destroy(self._h)
+            L.lib.tf_destroy(self._h)          # waits for a frame copy in flight
             self._h = L.handle_t()
+            for p in self._pinned:
+                L.lib.tf_host_free(p)
+            self._pinned = []
 
     def __del__(self):
         try:
@@ -175,6 +179,31 @@ class Strip(object):
         out = np.empty((self.ny, self.nx), dtype=np.float64)
         L.check(L.lib.tf_chan_get(self._h, int(which), L.ptr(out, C.c_double)))
         return out
+
+    def frame(self, which, swap_endian=False, out=None, wait=True):
+        """One field as the float32 [ny, nx] frame the reference appends to an
+        .rts stack (rts_files.py:313-396), rounded and byte-swapped on the
+        device.  With wait=False the copy is still in flight on return; call
+        frame_wait() before reading `out` (give a pinned_frame() for a truly
+        asynchronous copy)."""
+        if out is None:
+            out = np.empty((self.ny, self.nx), dtype=np.float32)
+        assert out.dtype == np.float32 and out.size == self.ny * self.nx and out.flags.c_contiguous
+        L.check(L.lib.tf_chan_frame(self._h, int(which), int(bool(swap_endian)),
+                                    L.ptr(out, C.c_float), 0 if wait else 1))
+        return out
+
+    def frame_wait(self):
+        L.check(L.lib.tf_chan_frame_wait(self._h))
+
+    def pinned_frame(self):
+        """A page-locked float32 [ny, nx] array (freed with the strip)."""
+        p = C.c_void_p()
+        nbytes = 4 * self.ny * self.nx
+        L.check(L.lib.tf_host_alloc(nbytes, C.byref(p)))
+        self._pinned.append(p)
+        buf = (C.c_float * (self.ny * self.nx)).from_address(p.value)
+        return np.frombuffer(buf, dtype=np.float32).reshape(self.ny, self.nx)
 
     def minmax(self):
         out = np.zeros(6, dtype=np.float64)

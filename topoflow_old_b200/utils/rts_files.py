@@ -59,6 +59,13 @@ class rts_file(object):
         out.tofile(self.rts_unit)
         self.time_index += 1
 
+    def add_frame(self, frame):
+        """Append a frame that already is in the file's dtype and byte order
+        (converted on the device, engine.Strip.frame)."""
+        assert frame.dtype == np.dtype(self.dtype) and frame.size == self.nx * self.ny
+        frame.tofile(self.rts_unit)
+        self.time_index += 1
+
     def get_grid(self, time_index, dtype=None):
         self.rts_unit.seek(time_index * self.grid_size)
         grid = np.fromfile(self.rts_unit, count=self.nx * self.ny, dtype=dtype or self.dtype)
