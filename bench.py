@@ -400,8 +400,8 @@ def main():
     ap.add_argument('--size', type=int, default=16384, help='rows = columns per GPU')
     ap.add_argument('--wave', default='kinematic', choices=sorted(WAVE_ID))
     ap.add_argument('--generic', action='store_true', help='float64 parameter rasters (no packing)')
-    ap.add_argument('--cpu-size', type=int, default=1024)
-    ap.add_argument('--cpu-steps', type=int, default=20)
+    ap.add_argument('--cpu-size', type=int, default=2048)
+    ap.add_argument('--cpu-steps', type=int, default=25)
     ap.add_argument('--no-cpu', action='store_true')
     args = ap.parse_args()
     if args.impl == 'reference':

@@ -52,8 +52,14 @@ enum tf_field {
     TF_F_U_STAR = 10, TF_F_FROUDE = 11, TF_F_S_FREE = 12,   /* derived on call */
     TF_F_WIDTH = 13,    /* width with the overbank substitution applied       */
     TF_F_MUTATED = 14,  /* 1.0 where "top_width > dw" has fired, else 0.0     */
-    TF_F_COUNT = 15
+    TF_F_R = 15,        /* excess rain rate grid (only while R is a grid)      */
+    TF_F_COUNT = 16
 };
+
+/* the six fluxes update_R combines (channels_base.py:1103-1147), in the
+ * order the reference adds them: R = (P_rain + SM + GW + MR) - (ET + IN) */
+enum tf_forcing { TF_R_P_RAIN = 0, TF_R_SM = 1, TF_R_GW = 2, TF_R_MR = 3,
+                  TF_R_ET = 4, TF_R_IN = 5, TF_R_COUNT = 6 };
 
 /* D8 products that tf_d8_get understands (element type in brackets) */
 enum tf_d8_field {
@@ -159,6 +165,18 @@ int tf_chan_set_param(tf_handle h, int which, const double* grid,
 int tf_chan_init(tf_handle h, int wave, int law, double dt,
                  const double* da_rows, const int32_t* outlet_rc,
                  int n_outlets, int allow_packed);
+
+/* update_R + update_R_integral on the device (channels_base.py:1103-1160).
+ * tf_chan_set_forcing hands over one of the six fluxes the framework sets
+ * into the component every step, as a dense [ny, nx] float64 grid or (grid ==
+ * NULL) a scalar; tf_chan_assemble_R then forms
+ *     R = (P_rain + SM + GW + MR) - (ET + IN)
+ * cell by cell in that order of operations (a scalar flux broadcasts as in
+ * NumPy), leaves it where the step kernels read it, and returns in sum_out
+ * (optional) the vol_R increment sum((R*da)*dt).  With all six scalar, R
+ * stays a scalar kernel argument and no grid is touched. */
+int tf_chan_set_forcing(tf_handle h, int which, const double* grid, double scalar);
+int tf_chan_assemble_R(tf_handle h, double* sum_out);
 
 /* Density of water [kg m-3] used for tau and u_star (the met component's
  * 'water-liquid__mass-per-volume_density', channels_base.py:165, :1577). */

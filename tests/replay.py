@@ -182,6 +182,11 @@ class BmiPlaneChannels(cp.Component):
             comp.set_values(long_name, getattr(div, attr))
         for long_name in ('sinks__count', 'sources__count'):
             comp.set_values(long_name, np.array(0, dtype='int32'))
+        for long_name in ('snowpack__melt_volume_flux', 'land_surface_water__baseflow_volume_flux',
+                          'glacier_ice__melt_volume_flux', 'land_surface_water__evaporation_volume_flux',
+                          'soil_surface_water__infiltration_volume_flux'):
+            comp.set_values(long_name, cp.scalar(0))           # Disabled providers: 0-d zeros
+        comp.set_values('water-liquid__mass-per-volume_density', cp.scalar(1000.0))
         comp.initialize(cfg_file=cfg_file, SILENT=True)
         self.comp, self.dt, self.time = comp, comp.dt, comp.time
         self.time_index, self.status = 0, 'initialized'

@@ -290,3 +290,66 @@ def test_output_frames_are_the_float32_grids_the_reference_writes():
         assert not np.array_equal(np.float32(s.get(L.F_Q)), want_q)   # the state did move on
     finally:
         s.close()
+
+
+def test_update_R_on_the_device():
+    """tf_chan_set_forcing / tf_chan_assemble_R against update_R and
+    update_R_integral (channels_base.py:1103-1160) with a mix of grid and
+    scalar fluxes."""
+    from topoflow_old_b200 import _lib as L
+    c = make_case(97, 61, seed=17)
+    ch = oracle_for(c, 0, 2.0)
+    s = gpu_for(c, 0, 2.0)
+    rng = np.random.default_rng(5)
+    try:
+        grid = lambda scale: scale * rng.random((61, 97))
+        ch.P_rain, ch.SM, ch.GW = grid(3e-5), och.scalar(2e-6), grid(1e-6)
+        ch.MR, ch.ET, ch.IN = och.scalar(0.0), grid(5e-7), grid(4e-6)
+        vol_R = 0.0
+        for n in range(30):
+            if n == 10:                                   # a flux changes type mid-run
+                ch.SM = grid(1e-6)
+            if n == 20:
+                ch.IN = och.scalar(1e-6)
+            for k, v in enumerate((ch.P_rain, ch.SM, ch.GW, ch.MR, ch.ET, ch.IN)):
+                s.set_forcing(k, v)
+            vol_R += s.assemble_R()
+            want = (ch.P_rain + ch.SM + ch.GW + ch.MR) - (ch.ET + ch.IN)
+            if n in (0, 10, 20):
+                got = s.get(L.F_R)
+                assert np.array_equal(got.view(np.uint64), want.view(np.uint64))     # bit for bit
+            _, _, bad = s.step(1)
+            ch.update()
+        assert abs(vol_R - float(ch.vol_R)) <= 1e-12 * abs(float(ch.vol_R))
+        compare(s, ch, 'device R')
+        # all six scalar: R goes back to being a kernel argument
+        for k in range(6):
+            s.set_forcing(k, 1e-6 * (k + 1))
+        inc = s.assemble_R()
+        r = (1e-6 + 2e-6 + 3e-6 + 4e-6) - (5e-6 + 6e-6)
+        assert inc == ((r * float(c['da'])) * 2.0) * (97 * 61)
+        with pytest.raises(RuntimeError, match='R is a scalar'):
+            s.get(L.F_R)
+    finally:
+        s.close()
+
+
+@pytest.mark.parametrize('wave', ['kinematic', 'dynamic'])
+def test_raster_lengths_and_no_lookahead_paths(wave, monkeypatch):
+    """The fallbacks behind two layout decisions: ds / dw read from their
+    rasters (taken when they are not a function of the code and the row, e.g.
+    a sinuosity grid) and the L2 look-ahead switched off."""
+    monkeypatch.setenv('TF_B200_NO_LEN_ROWS', '1')
+    monkeypatch.setenv('TF_B200_PF_ROWS', '0')
+    c = make_case(131, 77, seed=23)
+    s, ch, _ = run_pair(c, WAVES[wave], 2.0 if wave == 'kinematic' else 0.5, 60)
+    s.close()
+
+
+def test_sinuosity_grid_takes_the_raster_path():
+    c = make_case(90, 70, seed=29)
+    rng = np.random.default_rng(3)
+    c['sinu'] = 1.0 + 0.5 * np.float64(np.float32(rng.random((70, 90))))
+    s, ch, _ = run_pair(c, 0, 2.0, 60)
+    assert s.timing()[3] >= 72.0            # ds and dw come from their rasters
+    s.close()

@@ -47,6 +47,8 @@ SIGNATURES = {
     'tf_chan_set_rho': (C.c_int, [handle_t, C.c_double]),
     'tf_chan_set_state': (C.c_int, [handle_t, C.c_int, _dp]),
     'tf_chan_set_R': (C.c_int, [handle_t, _dp, C.c_double, _dp]),
+    'tf_chan_set_forcing': (C.c_int, [handle_t, C.c_int, _dp, C.c_double]),
+    'tf_chan_assemble_R': (C.c_int, [handle_t, _dp]),
     'tf_chan_set_points': (C.c_int, [handle_t, C.c_int, _i32p, _i32p, _dp, C.c_int]),
     'tf_chan_step': (C.c_int, [handle_t, C.c_int, _dp, _dp, _i64p]),
     'tf_chan_step_async': (C.c_int, [handle_t, C.c_int]),
@@ -73,7 +75,8 @@ KINEMATIC, DIFFUSIVE, DYNAMIC = 0, 1, 2
 MANNING, LAW_OF_WALL = 0, 1
 P_WIDTH, P_TAN_ANGLE, P_COS_ANGLE, P_SLOPE, P_ROUGH, P_DS = range(6)
 (F_VOL, F_D, F_U, F_Q, F_QNEXT, F_F, F_RH, F_A_WET, F_P_WET, F_TAU, F_U_STAR,
- F_FROUDE, F_S_FREE, F_WIDTH, F_MUTATED) = range(15)
+ F_FROUDE, F_S_FREE, F_WIDTH, F_MUTATED, F_R) = range(16)
+R_P_RAIN, R_SM, R_GW, R_MR, R_ET, R_IN = range(6)
 D8_CODE, D8_PARENT_ID, D8_DS, D8_DW, D8_AREA, D8_INMASK, D8_RAW = range(7)
 PT_SOURCES, PT_SINKS, PT_CANALS_IN, PT_CANALS_OUT = range(4)
 

@@ -90,7 +90,7 @@ _VARS = (
 _DEVICE_FIELDS = {'vol': L.F_VOL, 'd': L.F_D, 'u': L.F_U, 'Q': L.F_Q, 'f': L.F_F,
                   'Rh': L.F_RH, 'A_wet': L.F_A_WET, 'P_wet': L.F_P_WET, 'tau': L.F_TAU,
                   'u_star': L.F_U_STAR, 'froude': L.F_FROUDE, 'S_free': L.F_S_FREE,
-                  'width': L.F_WIDTH, 'angle': L.F_MUTATED}
+                  'width': L.F_WIDTH, 'angle': L.F_MUTATED, 'R': L.F_R}
 
 
 class _DeviceGrid(object):
@@ -388,18 +388,32 @@ class channels_component(BMI_base.BMI_component):
 
     # -- per-step pieces ------------------------------------------------------------------
     def update_R(self):                                        # :1103-1147
-        self.R = (self.P_rain + self.SM + self.GW + self.MR) - (self.ET + self.IN)
+        """All six fluxes 0-d (what Disabled providers and a uniform rain give):
+        R is a host scalar and travels as a kernel argument.  Otherwise the
+        fluxes go to the device as they are and R is formed there
+        (tf_chan_assemble_R) -- no NumPy temporaries, no grid-sized R upload."""
+        fluxes = (self.P_rain, self.SM, self.GW, self.MR, self.ET, self.IN)
+        if all(np.size(v) == 1 for v in fluxes):
+            self.R = (self.P_rain + self.SM + self.GW + self.MR) - (self.ET + self.IN)
+            self.__dict__['_R_on_device'] = False
+        else:
+            strip = self.d8.strip
+            for k, v in enumerate(fluxes):                     # L.R_P_RAIN .. L.R_IN
+                strip.set_forcing(k, v)
+            self.__dict__['_R_on_device'] = True
 
     def update_R_integral(self):                               # :1151-1160
-        """Also hands R to the device: a scalar travels as a kernel argument,
-        a grid is uploaded (and summed there)."""
         strip = self.d8.strip
-        if np.size(self.R) == 1:
+        if not self.__dict__.get('_R_on_device', False):
             strip.set_R(float(self.R), want_sum=False)
             volume = np.double(self.R * self.da * self.dt)
             self.vol_R += (volume * self.rti.n_pixels)
         else:
-            self.vol_R += strip.set_R(self.R, want_sum=True)
+            self.vol_R += strip.assemble_R(want_sum=True)
+            host = self.__dict__['_host']
+            if np.ndim(host.get('R')) != 2:
+                host['R'] = np.zeros([self.ny, self.nx], dtype='float64')
+            self._stale.add('R')
         rho = getattr(self, 'rho_H2O', None)
         if rho is not None and np.size(rho) == 1:
             strip.set_rho(float(rho))

@@ -100,6 +100,7 @@ extern "C" int tf_create(int nx, int ny, int device, unsigned flags,
     tf_handle h = new tf_handle_s();
     h->device = device;
     { const char* e = getenv("TF_B200_DEBUG_SYNC"); h->debug_sync = e && e[0] == '1'; }
+    { const char* e = getenv("TF_B200_PF_ROWS"); if (e && e[0]) h->pf_rows = atoi(e); }
     Geom& g = h->g;
     g.nx = nx;
     g.ny = ny;

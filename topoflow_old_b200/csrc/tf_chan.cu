@@ -153,6 +153,58 @@ extern "C" int tf_chan_set_R(tf_handle h, const double* grid, double scalar, dou
     return 0;
 }
 
+extern "C" int tf_chan_set_forcing(tf_handle h, int which, const double* grid, double scalar) {
+    TF_TRY(use_device(h));
+    TF_CHECK(h->chan_ready, "tf_chan_set_forcing: call tf_chan_init first");
+    TF_CHECK(which >= 0 && which < TF_R_COUNT, "tf_chan_set_forcing: unknown flux %d", which);
+    if (!grid) {
+        h->forc_is_grid[which] = false;
+        h->forc_scalar[which] = scalar;
+        return 0;
+    }
+    TF_TRY(raster_alloc(h, h->forc[which], 0));
+    TF_TRY(raster_upload(h, h->forc[which], grid));
+    h->forc_is_grid[which] = true;
+    return 0;
+}
+
+extern "C" int tf_chan_assemble_R(tf_handle h, double* sum_out) {
+    TF_TRY(use_device(h));
+    TF_CHECK(h->chan_ready, "tf_chan_assemble_R: call tf_chan_init first");
+    const Geom& g = h->g;
+    bool any_grid = false;
+    for (int k = 0; k < TF_R_COUNT; ++k) any_grid = any_grid || h->forc_is_grid[k];
+    const double* v = h->forc_scalar;
+    if (!any_grid)
+        return tf_chan_set_R(h, nullptr,
+                             (((v[TF_R_P_RAIN] + v[TF_R_SM]) + v[TF_R_GW]) + v[TF_R_MR])
+                                 - (v[TF_R_ET] + v[TF_R_IN]), sum_out);
+    TF_TRY(raster_alloc(h, h->R, 0));
+    if (h->partial_cap < 6 * g.ny) {
+        if (h->partial) cudaFree(h->partial);
+        h->partial_cap = 6 * g.ny;
+        TF_CUDA(cudaMalloc((void**)&h->partial, sizeof(double) * h->partial_cap));
+    }
+    ForcingArgs fa;
+    for (int k = 0; k < TF_R_COUNT; ++k) {
+        fa.grid[k] = h->forc_is_grid[k] ? h->forc[k].p : nullptr;
+        fa.scalar[k] = h->forc_scalar[k];
+    }
+    ChanArgs a = chan_args(h, 0, g.ny);
+    k_assemble_R<<<g.ny, 256, 0, h->stream>>>(a, fa, h->R.p, h->partial);
+    TF_LAUNCHED(h, h->stream, "k_assemble_R");
+    h->R_is_grid = true;
+    if (sum_out) {
+        std::vector<double> part(g.ny);
+        TF_CUDA(cudaMemcpyAsync(part.data(), h->partial, sizeof(double) * g.ny, cudaMemcpyDeviceToHost, h->stream));
+        TF_CUDA(cudaStreamSynchronize(h->stream));
+        double s = 0.0;
+        for (int y = 0; y < g.ny; ++y) s += part[y];
+        *sum_out = s;
+    }
+    return 0;
+}
+
 extern "C" int tf_chan_set_points(tf_handle h, int kind, const int32_t* rows, const int32_t* cols,
                                   const double* values, int n) {
     TF_TRY(use_device(h));

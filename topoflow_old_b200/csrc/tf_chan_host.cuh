@@ -10,6 +10,8 @@ static inline ChanArgs chan_args(tf_handle h, int y_begin, int y_end) {
     const Geom& g = h->g;
     a.nx = g.nx; a.ny = g.ny; a.pitch = g.pitch;
     a.y_begin = y_begin; a.y_end = y_end;
+    if (h->pf_rows >= 0) a.pf_rows = h->pf_rows;
+    else a.pf_rows = 8;        // the next row of tiles: best at 8192^2 and 16384^2 (profiles/sweep_r01.txt)
     a.row_offset = g.row_offset; a.global_ny = g.global_ny;
     a.dt = h->dt; a.rho = h->rho;
     a.Q = h->Qcur; a.Qn = h->Qnext;
@@ -26,6 +28,7 @@ static inline ChanArgs chan_args(tf_handle h, int y_begin, int y_end) {
     a.w32 = h->w32.p; a.S32 = h->S32.p; a.n32 = h->n32.p; a.ds32 = h->ds32.p;
     a.aidx = h->aidx.p; a.lut = h->lut;
     a.kfac = h->kfac.p;
+    a.len_rows = h->len_rows;
     a.bad = h->bad;
     return a;
 }

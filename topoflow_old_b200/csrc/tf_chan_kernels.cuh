@@ -15,15 +15,32 @@
 #include "tf_chan_math.cuh"
 
 #ifndef TF_MINBLOCKS
-#define TF_MINBLOCKS 6
+#define TF_MINBLOCKS 4
 #endif
 #ifndef TF_MINBLOCKS_AB
 #define TF_MINBLOCKS_AB 5
+#endif
+// tuning switches; the defaults are the measured best (profiles/sweep_r01.txt)
+#ifndef TF_GATHER_UNROLL
+#define TF_GATHER_UNROLL 1
+#endif
+#ifndef TF_GATHER_UNROLL_DYN
+#define TF_GATHER_UNROLL_DYN 0   /* the momentum gather (3 loads per child) is faster as a loop */
+#endif
+#ifndef TF_LEAN_CHECKS
+#define TF_LEAN_CHECKS 1
+#endif
+#ifndef TF_PREFETCH
+#define TF_PREFETCH 9   /* bit 0: kfac of this tile, bit 3: look-ahead of a.pf_rows rows */
+#endif
+#ifndef TF_PROBE
+#define TF_PROBE 0      /* bit 0: skip the gather, bit 1: skip the arithmetic (timing experiments) */
 #endif
 
 struct ChanArgs {
     int nx, ny, pitch;
     int y_begin, y_end;            // rows this launch covers
+    int pf_rows;                   // L2 look-ahead distance in rows (0: off)
     int row_offset, global_ny;     // strip placement (bad-cell index, borders)
     double dt, rho;
     // state
@@ -50,6 +67,7 @@ struct ChanArgs {
     const uint8_t* aidx;
     const double* lut;             // [256] tan, [256] cos
     const double* kfac;            // kinematic + Manning: sqrt(S_bed) / n, float64
+    const float* len_rows;         // [8 * row]: ds {diag, E/W, N/S, -}, dw {diag, E/W, N/S, -}; NULL: read the rasters
     long long* bad;                // [0] depth, [1] velocity: min bad global index
 };
 
@@ -59,7 +77,7 @@ __device__ __forceinline__ void load_shape(const ChanArgs& a, int64_t i, double 
                                            double (&t)[CPT], double (&c)[CPT], double (&ds)[CPT]) {
     if (PACKED) {
         ld4(a.w32 + i, w);
-        ld4(a.ds32 + i, ds);
+        if (!a.len_rows) ld4(a.ds32 + i, ds);
         int ai[CPT];
         ld4(a.aidx + i, ai);
 #pragma unroll
@@ -75,6 +93,29 @@ __device__ __forceinline__ void load_shape(const ChanArgs& a, int64_t i, double 
     }
 }
 
+// Flow length ds and flow width dw are functions of the D8 code and of three
+// per-row lengths (update_flow_length_grid / update_flow_width_grid,
+// d8_global.py:863-1004; ds then scaled by the sinuosity, channels_base.py:882).
+// When the host has verified that for every cell (tf_chan_layout.cu), the
+// packed layout reads the code it needs anyway and 32 bytes per row instead of
+// two float32 rasters: 8 bytes per cell and step less from HBM.
+template <bool PACKED>
+__device__ __forceinline__ void load_lengths(const ChanArgs& a, int64_t i, int y, const int (&code)[CPT],
+                                             double (&ds)[CPT], double (&dwv)[CPT]) {
+    if (PACKED && a.len_rows) {
+        const float4 rs = __ldg(reinterpret_cast<const float4*>(a.len_rows + 8 * y));
+        const float4 rw = __ldg(reinterpret_cast<const float4*>(a.len_rows + 8 * y + 4));
+#pragma unroll
+        for (int k = 0; k < CPT; ++k) {
+            const int cd = code[k];                      // 1,4,16,64 diagonal; 2,32 E/W; 8,128 N/S; 0
+            ds[k] = (double)((cd & 0x55) ? rs.x : ((cd & 0x88) ? rs.z : rs.y));
+            dwv[k] = (double)((cd & 0x55) ? rw.x : ((cd & 0x22) ? rw.y : rw.z));
+        }
+    } else {
+        ld4(a.dw + i, dwv);                              // ds came with load_shape
+    }
+}
+
 template <bool PACKED>
 __device__ __forceinline__ void load_slope_rough(const ChanArgs& a, int64_t i, double (&S)[CPT],
                                                  double (&n)[CPT]) {
@@ -84,6 +125,44 @@ __device__ __forceinline__ void load_slope_rough(const ChanArgs& a, int64_t i, d
     } else {
         ld4(a.S64 + i, S);
         ld4(a.n64 + i, n);
+    }
+}
+
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
+// Software pipelining through L2: ask for the cells a later wave of blocks
+// will read (pf_rows rows further south) so that its loads find them in L2
+// instead of paying a DRAM round trip per dependent load.  No registers held.
+template <bool PACKED>
+__device__ __forceinline__ void prefetch_shape(const ChanArgs& a, int64_t j) {
+    if (!(PACKED && a.len_rows)) prefetch_l2(a.dw + j);
+    if (PACKED) {
+        prefetch_l2(a.w32 + j);
+        if (!a.len_rows) prefetch_l2(a.ds32 + j);
+    } else {
+        prefetch_l2(a.w64 + j); prefetch_l2(a.ds64 + j);
+        prefetch_l2(a.tan64 + j); prefetch_l2(a.cos64 + j);
+    }
+}
+template <bool PACKED>
+__device__ __forceinline__ void prefetch_slope_rough(const ChanArgs& a, int64_t j) {
+    if (PACKED) { prefetch_l2(a.S32 + j); prefetch_l2(a.n32 + j); }
+    else { prefetch_l2(a.S64 + j); prefetch_l2(a.n64 + j); }
+}
+// what volume_and_depth reads (kinematic step, phase A)
+template <bool PACKED>
+__device__ __forceinline__ void prefetch_ahead_a(const ChanArgs& a, int64_t j) {
+    prefetch_l2(a.Q + j);
+    prefetch_l2(a.vol + j);
+    prefetch_shape<PACKED>(a, j);
+    if (a.Rgrid) prefetch_l2(a.Rgrid + j);
+    if ((threadIdx.x & 7) == 0) {           // byte streams: one request per 32-byte sector
+        prefetch_l2(a.code + j);
+        prefetch_l2(a.inmask + j);
+        prefetch_l2(a.mstate + j);
+        if (PACKED) prefetch_l2(a.aidx + j);
     }
 }
 
@@ -127,7 +206,7 @@ __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int 
     ld4(a.inmask + i, mask);
     ld4c(a.mstate + i, ms);
     load_shape<PACKED>(a, i, w, t, c, ds);
-    ld4(a.dw + i, dwv);
+    load_lengths<PACKED>(a, i, y, code, ds, dwv);
     double R[CPT];
     if (a.Rgrid) ld4(a.Rgrid + i, R);
     else {
@@ -142,15 +221,41 @@ __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int 
         apply_overbank(a, m[k], dwv[k], w[k], t[k], c[k]);
         double acc = v[k] + (R[k] * da) * dt;                  // :1334
         int mk = mask[k];
+#if TF_PROBE & 1        /* timing experiment: no inflow gather */
+        acc += (double)mk;
+        mk = 0;
+#endif
+#if TF_GATHER_UNROLL
+        // the k = 1..8 adds of :1346-1361 in order, each predicated on its bit
+        // of the mask; offsets are compile-time forms of the pitch, and the
+        // east / west child of a cell pair is already in registers
+        {
+            const double* q = a.Q + i + k;
+            const int64_t p = a.pitch;
+            if (mk & 1) acc += dt * __ldg(q + (p - 1));
+            if (mk & 2) acc += dt * ((CPT == 2 && k == 1) ? Q[0] : __ldg(q - 1));
+            if (mk & 4) acc += dt * __ldg(q - (p + 1));
+            if (mk & 8) acc += dt * __ldg(q - p);
+            if (mk & 16) acc += dt * __ldg(q - (p - 1));
+            if (mk & 32) acc += dt * ((CPT == 2 && k == 0) ? Q[1] : __ldg(q + 1));
+            if (mk & 64) acc += dt * __ldg(q + (p + 1));
+            if (mk & 128) acc += dt * __ldg(q + p);
+        }
+#else
         while (mk) {                                           // :1346-1361
             const int j = __ffs(mk) - 1;
             mk &= mk - 1;
             acc += dt * __ldg(a.Q + i + k + child_offset(j, a.pitch));
         }
+#endif
         acc -= Q[k] * dt;                                      // :1366
         acc = np_max0(acc);                                    // :1375
         v[k] = acc;
+#if TF_PROBE & 2        /* timing experiment: no depth arithmetic */
+        double dd = acc * w[k] + t[k] * ds[k];
+#else
         double dd = chan_depth(acc, w[k], t[k], ds[k]);
+#endif
         if (code[k] == 0) dd = 0.0;                            // :1511
         d[k] = np_max0(dd);                                    // :1526
     }
@@ -191,24 +296,59 @@ k_step_kinematic(const ChanArgs a) {
     const int64_t i = (int64_t)y * a.pitch + x4;
     double Q[CPT], v[CPT], d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT], S[CPT], n[CPT], u[CPT], Qn[CPT];
     int code[CPT], m[CPT], ms[CPT];
-    volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
+#if TF_PREFETCH & 1
+    // the velocity factor is read after the depth arithmetic (no registers to
+    // hold it until then): start its trip from DRAM now, so that read hits L2
+    if (KF) prefetch_l2(a.kfac + i);
+#endif
+#if TF_PREFETCH & 2
+    // the tile's halo rows of Q, which no warp of this block loads as its own
+    if (threadIdx.y == 0) prefetch_l2(a.Q + i - a.pitch);
+    if (threadIdx.y == 7) prefetch_l2(a.Q + i + a.pitch);
+#endif
+#if TF_PREFETCH & 8
+    if (a.pf_rows > 0 && y + a.pf_rows < a.y_end) {
+        const int64_t j = i + (int64_t)a.pf_rows * a.pitch;
+        prefetch_ahead_a<PACKED>(a, j);
+        if (KF) prefetch_l2(a.kfac + j);
+        else prefetch_slope_rough<PACKED>(a, j);
+    }
+#endif
+#if TF_PREFETCH & 4
     if (KF) ld4(a.kfac + i, S);
-    else load_slope_rough<PACKED>(a, i, S, n);
+#endif
+    volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
+#if !(TF_PREFETCH & 4)
+    if (KF) ld4(a.kfac + i, S);
+#endif
+    if (!KF) load_slope_rough<PACKED>(a, i, S, n);
     bool bad_d = false, bad_u = false;
     int bx = 0;
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
         const bool noflow = (code[k] == 0);
+#if TF_PROBE & 2        /* timing experiment: no velocity arithmetic */
+        XSection xs; xs.A_wet = d[k] + c[k]; xs.Rh = w[k];
+        double uu = xs.Rh * S[k];
+#else
         const XSection xs = chan_xsection(d[k], w[k], t[k], c[k], noflow);
         double uu = KF ? pow_two_thirds(xs.Rh) * S[k]
                        : chan_velocity<LAW>(xs.Rh, S[k], n[k], d[k]);   // kinematic: S = S_bed
+#endif
         if (noflow) uu = 0.0;                                      // :1783-1791
         u[k] = uu;
         Qn[k] = uu * xs.A_wet;                                     // :1188 of the next step
+#if TF_LEAN_CHECKS
+        // d = np_max0(.) is never negative, so "bad" is NaN or +inf; padding
+        // cells (x >= nx) hold a harmless shape with code 0 and stay at d = u = 0
+        bad_d = bad_d || !(d[k] <= 1.7976931348623157e308);
+        bad_u = bad_u || !(uu >= 0.0 && uu <= 1.7976931348623157e308);
+#else
         if (x4 + k < a.nx) {
             if (bad_value(d[k]) && !bad_d) { bad_d = true; bx = x4 + k; }
             if (bad_value(uu) && !bad_u) { bad_u = true; if (!bad_d) bx = x4 + k; }
         }
+#endif
     }
     st4(a.vol + i, v);
     st4(a.d + i, d);
@@ -240,6 +380,10 @@ k_phase_a(const ChanArgs a) {
     const int64_t i = (int64_t)y * a.pitch + x4;
     double Q[CPT], v[CPT], d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT];
     int code[CPT], m[CPT], ms[CPT];
+#if TF_PREFETCH & 8
+    if (a.pf_rows > 0 && y + a.pf_rows < a.y_end)
+        prefetch_ahead_a<PACKED>(a, i + (int64_t)a.pf_rows * a.pitch);
+#endif
     volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
     st4(a.vol + i, v);
     st4(a.d + i, d);

@@ -32,11 +32,26 @@ k_phase_b(const ChanArgs a) {
     const int64_t i = (int64_t)y * a.pitch + x4;
     double d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT], S[CPT], n[CPT], u[CPT], Qn[CPT];
     int code[CPT], ms[CPT];
+#if TF_PREFETCH & 8
+    if (a.pf_rows > 0 && y + a.pf_rows < a.y_end) {
+        const int64_t j = i + (int64_t)a.pf_rows * a.pitch;
+        prefetch_l2(a.d + j);
+        prefetch_shape<PACKED>(a, j);
+        prefetch_slope_rough<PACKED>(a, j);
+        if (WAVE == 2) { prefetch_l2(a.Q + j); prefetch_l2(a.vol + j); prefetch_l2(a.u_old + j); }
+        if ((threadIdx.x & 7) == 0) {
+            prefetch_l2(a.code + j);
+            prefetch_l2(a.mstate + j);
+            if (PACKED) prefetch_l2(a.aidx + j);
+            if (WAVE == 2) prefetch_l2(a.inmask + j);
+        }
+    }
+#endif
     ld4c(a.d + i, d);
     ld4(a.code + i, code);
     ld4c(a.mstate + i, ms);
     load_shape<PACKED>(a, i, w, t, c, ds);
-    ld4(a.dw + i, dwv);
+    load_lengths<PACKED>(a, i, y, code, ds, dwv);
     load_slope_rough<PACKED>(a, i, S, n);
     double Q[CPT], v[CPT], uo[CPT];
     int mask[CPT];
@@ -69,6 +84,33 @@ k_phase_b(const ChanArgs a) {
             const double dM = ((grav - fric) - Qtrm) * dt;         // :214
             double M = (u0 * v[k]) + dM;                           // :222
             int mk = mask[k];
+#if TF_GATHER_UNROLL_DYN
+            // the k = 1..8 momentum adds of :244-259 in order, each predicated on
+            // its bit of the mask; the east / west child of a pair is in registers
+            {
+                const int64_t c0 = i + k, p = a.pitch;
+#define TF_DYN_TERM(ci)                                                              \
+    {                                                                                \
+        const double uc = (a.d[ci] > 0.0) ? __ldg(a.u_old + (ci)) : 0.0;             \
+        M += (uc * __ldg(a.Q + (ci))) * dt;                                          \
+    }
+                if (mk & 1) TF_DYN_TERM(c0 + (p - 1))
+                if (mk & 2) {
+                    if (CPT == 2 && k == 1) M += (((d[0] > 0.0) ? uo[0] : 0.0) * Q[0]) * dt;
+                    else TF_DYN_TERM(c0 - 1)
+                }
+                if (mk & 4) TF_DYN_TERM(c0 - (p + 1))
+                if (mk & 8) TF_DYN_TERM(c0 - p)
+                if (mk & 16) TF_DYN_TERM(c0 - (p - 1))
+                if (mk & 32) {
+                    if (CPT == 2 && k == 0) M += (((d[1] > 0.0) ? uo[1] : 0.0) * Q[1]) * dt;
+                    else TF_DYN_TERM(c0 + 1)
+                }
+                if (mk & 64) TF_DYN_TERM(c0 + (p + 1))
+                if (mk & 128) TF_DYN_TERM(c0 + p)
+#undef TF_DYN_TERM
+            }
+#else
             while (mk) {                                           // :244-259
                 const int j = __ffs(mk) - 1;
                 mk &= mk - 1;
@@ -76,6 +118,7 @@ k_phase_b(const ChanArgs a) {
                 const double uc = (a.d[ci] > 0.0) ? __ldg(a.u_old + ci) : 0.0;
                 M += (uc * __ldg(a.Q + ci)) * dt;
             }
+#endif
             M = np_max0(M);                                        // :312
             uu = np_max0(M * vinv);                                // :318-331
         }
@@ -238,6 +281,38 @@ k_sum_R(const ChanArgs a, double* partial) {
     const double da = a.da_rows[y];
     for (int x = threadIdx.x; x < a.nx; x += blockDim.x)
         acc += (a.Rgrid[(int64_t)y * a.pitch + x] * da) * a.dt;
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) partial[y] = sh[0];
+}
+
+struct ForcingArgs {
+    const double* grid[TF_R_COUNT];   // cell (0,0) of each flux raster, or NULL
+    double scalar[TF_R_COUNT];
+};
+
+// update_R (:1103-1147) and, in the same pass, the row sums of (R*da)*dt for
+// update_R_integral (:1151-1160).  One block per row.
+static __global__ void __launch_bounds__(256)
+k_assemble_R(const ChanArgs a, const ForcingArgs fa, double* __restrict__ R, double* partial) {
+    __shared__ double sh[256];
+    const int y = blockIdx.x;
+    const double da = a.da_rows[y];
+    double acc = 0.0;
+    for (int x = threadIdx.x; x < a.nx; x += blockDim.x) {
+        const int64_t i = (int64_t)y * a.pitch + x;
+        double v[TF_R_COUNT];
+#pragma unroll
+        for (int k = 0; k < TF_R_COUNT; ++k) v[k] = fa.grid[k] ? __ldcs(fa.grid[k] + i) : fa.scalar[k];
+        const double r = (((v[TF_R_P_RAIN] + v[TF_R_SM]) + v[TF_R_GW]) + v[TF_R_MR])
+                         - (v[TF_R_ET] + v[TF_R_IN]);
+        R[i] = r;
+        acc += (r * da) * a.dt;
+    }
     sh[threadIdx.x] = acc;
     __syncthreads();
     for (int s = 128; s > 0; s >>= 1) {

@@ -115,6 +115,35 @@ int chan_layout_init(tf_handle h, int allow_packed) {
     {
         std::vector<float> dw((size_t)g.n_alloc);
         TF_CUDA(cudaMemcpy(dw.data(), h->dw.base, sizeof(float) * (size_t)g.n_alloc, cudaMemcpyDeviceToHost));
+        // ds and dw as functions of the code and three lengths per row: use
+        // them only if that reproduces every cell of both grids exactly
+        if (h->len_rows) { cudaFree(h->len_rows); h->len_rows = nullptr; }
+        if (packed && !getenv("TF_B200_NO_LEN_ROWS")) {
+            std::vector<uint8_t> code((size_t)g.n_alloc);
+            TF_CUDA(cudaMemcpy(code.data(), h->code.base, (size_t)g.n_alloc, cudaMemcpyDeviceToHost));
+            std::vector<float> rows((size_t)8 * g.ny, 0.0f);
+            bool ok = true;
+            for (int y = 0; y < g.ny && ok; ++y) {
+                const uint8_t* cr = code.data() + g.origin + (int64_t)y * g.pitch;
+                const float* wr = dw.data() + g.origin + (int64_t)y * g.pitch;
+                float* r = rows.data() + (size_t)8 * y;
+                bool have[6] = {false, false, false, false, false, false};
+                for (int x = 0; x < g.nx; ++x) {
+                    const int cd = cr[x];
+                    const int ks = (cd & 0x55) ? 0 : ((cd & 0x88) ? 2 : 1);        // ds class
+                    const int kw = (cd & 0x55) ? 4 : ((cd & 0x22) ? 5 : 6);        // dw class
+                    const float vs = (float)hp_at(D, (size_t)y * g.nx + x), vw = wr[x];
+                    if (!have[ks]) { have[ks] = true; r[ks] = vs; }
+                    else if (r[ks] != vs) { ok = false; break; }
+                    if (!have[kw - 1]) { have[kw - 1] = true; r[kw] = vw; }
+                    else if (r[kw] != vw) { ok = false; break; }
+                }
+            }
+            if (ok) {
+                TF_CUDA(cudaMalloc((void**)&h->len_rows, sizeof(float) * rows.size()));
+                TF_CUDA(cudaMemcpy(h->len_rows, rows.data(), sizeof(float) * rows.size(), cudaMemcpyHostToDevice));
+            }
+        }
         for (int y = -1; y <= g.ny; ++y) {
             float* row = dw.data() + g.origin + (int64_t)y * g.pitch;
             for (int x = 0; x < g.pitch; ++x)

@@ -180,6 +180,9 @@ int chan_derive_to_scratch(tf_handle h, int which, const double** src_out) {
         case TF_F_U: *src_out = h->u.p; return 0;
         case TF_F_Q: *src_out = h->Qcur; return 0;
         case TF_F_QNEXT: *src_out = h->Qnext; return 0;
+        case TF_F_R:
+            TF_CHECK(h->R_is_grid && h->R.p, "tf_chan_get: R is a scalar right now (%.17g)", h->R_scalar);
+            *src_out = h->R.p; return 0;
         default: break;
     }
     TF_CHECK(!(which == TF_F_S_FREE && h->wave == TF_KINEMATIC),
@@ -238,15 +241,16 @@ extern "C" int tf_chan_minmax(tf_handle h, double* out6) {
 static double layout_bytes_per_cell(tf_handle h) {
     // bytes the step kernels address per cell-update in the current layout
     double b = 0.0;
-    const double shape = h->packed ? (4 + 4 + 1) : (8 + 8 + 8 + 8);   // w, ds, angle
+    const double shape = h->packed ? ((h->len_rows ? 4 : 4 + 4) + 1) : (8 + 8 + 8 + 8);   // w, ds, angle
     const double sr = h->packed ? 8 : 16;                            // S, roughness
     const double R = h->R_is_grid ? 8 : 0;
+    const double dw = (h->packed && h->len_rows) ? 0 : 4;            // derived from the code
     if (h->wave == TF_KINEMATIC) {
-        b = 8 /*Q*/ + 8 /*vol r*/ + 1 + 1 + 1 /*code, mask, mstate*/ + shape + 4 /*dw*/
+        b = 8 /*Q*/ + 8 /*vol r*/ + 1 + 1 + 1 /*code, mask, mstate*/ + shape + dw
             + (h->kfac.p ? 8 : sr) + R + 32 /*vol, d, u, Qnext w*/;
     } else {
-        const double A = 8 + 8 + 3 + shape + 4 + R + 16;              // phase A
-        double B = 8 /*d*/ + 2 + shape + 4 + sr + 16;                 // phase B: u, Qn
+        const double A = 8 + 8 + 3 + shape + dw + R + 16;             // phase A
+        double B = 8 /*d*/ + 2 + shape + dw + sr + 16;                // phase B: u, Qn
         if (h->wave == TF_DYNAMIC) B += 8 + 8 + 8 + 1;                // Q, vol, u_old, mask
         b = A + B;
     }
@@ -275,15 +279,16 @@ extern "C" int tf_chan_timing(tf_handle h, double* out4) {
 int chan_free(tf_handle h) {
     raster_free(h->vol); raster_free(h->d); raster_free(h->u); raster_free(h->u2);
     raster_free(h->Qa); raster_free(h->Qb); raster_free(h->R);
+    for (int k = 0; k < TF_R_COUNT; ++k) { raster_free(h->forc[k]); h->forc_is_grid[k] = false; }
     raster_free(h->f); raster_free(h->mstate);
     raster_free(h->w64); raster_free(h->tan64); raster_free(h->cos64);
     raster_free(h->S64); raster_free(h->n64); raster_free(h->ds64); raster_free(h->kfac);
     raster_free(h->w32); raster_free(h->S32); raster_free(h->n32); raster_free(h->ds32);
     raster_free(h->aidx);
-    void* ptrs[] = {h->lut, h->ds_rows, h->da_rows, h->outlet_idx, h->taps, h->canal_taps,
+    void* ptrs[] = {h->lut, h->len_rows, h->da_rows, h->outlet_idx, h->taps, h->canal_taps,
                     h->partial, h->scratch64, h->pts_tmp};
     for (void* p : ptrs) if (p) cudaFree(p);
-    h->lut = nullptr; h->ds_rows = nullptr; h->da_rows = nullptr; h->outlet_idx = nullptr;
+    h->lut = nullptr; h->len_rows = nullptr; h->da_rows = nullptr; h->outlet_idx = nullptr;
     h->taps = nullptr; h->canal_taps = nullptr; h->partial = nullptr; h->scratch64 = nullptr;
     h->pts_tmp = nullptr;
     for (int k = 0; k < 4; ++k) {

@@ -139,6 +139,9 @@ struct tf_handle_s {
     double *ucur = nullptr, *unext = nullptr;   // dynamic wave double buffer
     bool R_is_grid = false;
     double R_scalar = 0.0;
+    Raster<double> forc[TF_R_COUNT];      // fluxes of update_R handed over as grids
+    double forc_scalar[TF_R_COUNT] = {0, 0, 0, 0, 0, 0};
+    bool forc_is_grid[TF_R_COUNT] = {false, false, false, false, false, false};
     Raster<uint8_t> mstate;               // bit0 mutated, bit1 pending
     // parameters, generic layout (float64)
     Raster<double> w64, tan64, cos64, S64, n64, ds64;
@@ -147,7 +150,7 @@ struct tf_handle_s {
     Raster<float> w32, S32, n32, ds32;
     Raster<uint8_t> aidx;
     double* lut = nullptr;                // device [2*256]: tan, cos
-    float* ds_rows = nullptr;             // device [3*(ny+2)]: diag, ew, ns
+    float* len_rows = nullptr;            // device [8*ny]: ds {diag, E/W, N/S, -}, dw {diag, E/W, N/S, -}
     // outlets, diversions
     int n_outlets = 0;
     int64_t* outlet_idx = nullptr;        // device
@@ -176,6 +179,7 @@ struct tf_handle_s {
     // ---- communication ------------------------------------------------------
     void* nccl_comm = nullptr;
     int rank = 0, nranks = 1;
+    int pf_rows = -1;                     // L2 look-ahead rows; -1 = from the grid width (TF_B200_PF_ROWS)
     bool debug_sync = false;              // TF_B200_DEBUG_SYNC=1: sync + check after every launch
 };
 

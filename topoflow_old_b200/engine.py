@@ -150,6 +150,22 @@ class Strip(object):
             L.check(L.lib.tf_chan_set_R(self._h, L.ptr(g, C.c_double), 0.0, sp))
         return s.value
 
+    def set_forcing(self, which, value):
+        """One of the six fluxes of update_R (L.R_P_RAIN ...): 0-d or [ny, nx]."""
+        if np.ndim(value) == 0 or np.size(value) == 1:
+            L.check(L.lib.tf_chan_set_forcing(self._h, int(which), None, float(np.asarray(value).reshape(-1)[0])))
+        else:
+            g = _f64(value)
+            assert g.shape == (self.ny, self.nx)
+            L.check(L.lib.tf_chan_set_forcing(self._h, int(which), L.ptr(g, C.c_double), 0.0))
+
+    def assemble_R(self, want_sum=True):
+        """R = (P_rain + SM + GW + MR) - (ET + IN) on the device; returns the
+        vol_R increment sum((R*da)*dt) when asked."""
+        out = C.c_double(0.0)
+        L.check(L.lib.tf_chan_assemble_R(self._h, C.byref(out) if want_sum else None))
+        return out.value if want_sum else None
+
     def set_points(self, kind, rows, cols, values):
         rows = np.ascontiguousarray(np.atleast_1d(rows), dtype=np.int32)
         cols = np.ascontiguousarray(np.atleast_1d(cols), dtype=np.int32)
