@@ -374,9 +374,11 @@ def run_reference(args):
         'unit': 'cell-updates/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': el / args.steps * 1e3, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-        'config': {'workload': 'synthetic fractal DEM, %s-wave channels, Manning, uniform rain pulse; '
-                               'CPU sample %dx%d of the %dx%d workload' % (args.wave, size, size, args.size, args.size),
-                   'wave': args.wave},
+        'config': {'workload': 'synthetic %dx%d fractal DEM per GPU, %s-wave channels, Manning, '
+                               'uniform rain pulse, D8 built on GPU' % (args.size, args.size, args.wave),
+                   'grid_per_gpu': [args.size, args.size], 'wave': args.wave,
+                   'sample': 'each step = one update of the reference algorithm on a %dx%d sample of '
+                             'that workload (same generator, same parameters), host cores only' % (size, size)},
         'cpu_baseline': {'value': v, 'unit': 'cell-updates/s', 'cores': 1, 'kind': 'port',
                          'sample': '%d steps on a %dx%d grid; NumPy restatement of channels_base.update() '
                                    '(the reference itself is Python 2.7 only; python2.7 %s)' % (
