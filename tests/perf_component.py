@@ -10,7 +10,7 @@ import time
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))   # lives under tests/: it times the oracle next to the component
 sys.path.insert(0, ROOT)
 from oracle import channels as och          # noqa: E402  (baseline leg only)
 from tests import replay                    # noqa: E402
