@@ -17,9 +17,11 @@ Parity status: PINNED.
                     every column of Case1_0D-{Q,d,u}.txt digit for digit and
                     all 60 frames of Case1_2D-Q.rts bit for bit (this pins
                     update_diversions, channels_base.py:1226-1297) -- and, driven through a restatement of the EMELI loop
-                    (oracle/coupling.py), the shipped Treynor hydrographs of
-                    Test1_kin_wave and Test2_diff_wave digit for digit, with
-                    Q/u/d peaks equal to the console log to 12 digits;
+                    (oracle/coupling.py), the shipped Treynor runs Test1_kin_wave,
+                    Test2_diff_wave and Test2_diff_wave_dt=6s: hydrographs digit
+                    for digit, every frame of their float32 Q grid stacks
+                    (158-159 frames x 1276 cells) bit for bit, Q/u/d peaks equal
+                    to the console log to 12 digits;
                     Test12_dynam_wave identical through the peak, within 1e-5
                     on the recession (glibc vs the 2017 macOS libm)
 see tests/test_oracle_*.py.

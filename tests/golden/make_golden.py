@@ -24,8 +24,9 @@ TREYNOR_IN = ['Treynor.rti', 'Treynor_DEM.rtg', 'Treynor_flow.rtg',
               'June_20_67_d8_global.cfg', 'June_20_67_path_info.cfg',
               'June_20_67_outlets.txt', 'June_20_67_rain_rates.txt',
               'June_20_67_meteorology.cfg', 'June_20_67_infil_green_ampt.cfg']
-TREYNOR_OUT = {'Test1_kin_wave': ['June_20_67_0D-Q.txt', 'June_20_67_2D-Q.rti'],
-               'Test2_diff_wave': ['June_20_67_0D-Q.txt'],
+TREYNOR_OUT = {'Test1_kin_wave': ['June_20_67_0D-Q.txt', 'June_20_67_2D-Q.rti', 'June_20_67_2D-Q.rts'],
+               'Test2_diff_wave': ['June_20_67_0D-Q.txt', 'June_20_67_2D-Q.rts'],
+               'Test2_diff_wave_dt=6s': ['June_20_67_0D-Q.txt', 'June_20_67_2D-Q.rts'],
                'Test12_dynam_wave': ['June_20_67_0D-Q.txt']}
 PLANE_IN = ['plane.rti', 'plane_DEM.rtg', 'plane_slope.rtg', 'plane_flow.rtg',
             'plane_chan-a.rtg', 'plane_chan-n.rtg', 'plane_chan-w.rtg',
@@ -83,7 +84,7 @@ def main():
     for case, files in TREYNOR_OUT.items():
         for f in files:
             cp(os.path.join(t, '00_Output_Files', case, f),
-               os.path.join(HERE, 'treynor', 'out_' + case, f))
+               os.path.join(HERE, 'treynor', 'out_' + case.replace('=', ''), f))
         scal[case] = log_scalars(os.path.join(t, '00_Output_Files', case,
                                               '00_Full_Output.txt'))
     json.dump(scal, open(os.path.join(HERE, 'treynor', 'log_scalars.json'), 'w'),

@@ -13,7 +13,18 @@ from oracle import d8 as od8
 OUTLETS = [(34, 16), (32, 16), (37, 19), (26, 14), (30, 15)]     # June_20_67_outlets.txt (row, col)
 CASES = {'kinematic': ('out_Test1_kin_wave', 'Test1_kin_wave', 2.0, 159),
          'diffusive': ('out_Test2_diff_wave', 'Test2_diff_wave', 2.0, 158),
+         'diffusive_dt6': ('out_Test2_diff_wave_dt6s', 'Test2_diff_wave_dt=6s', 6.0, 158),
          'dynamic': ('out_Test12_dynam_wave', 'Test12_dynam_wave', 0.5, 140)}
+
+
+def wave_of(case):
+    return case.split('_')[0]
+
+
+def golden_stack(golden_dir, case):
+    """<case>_2D-Q.rts of a shipped run: float32 MSB frames of 44 x 29, one per minute."""
+    p = os.path.join(golden_dir, 'treynor', CASES[case][0], 'June_20_67_2D-Q.rts')
+    return np.fromfile(p, dtype='>f4').reshape(-1, 44, 29).astype(np.float32)
 GREEN_AMPT = dict(Ks=7.2e-06, Ki=1e-07, qs=0.485, qi=0.375808, G=0.724)   # June_20_67_infil_green_ampt.cfg
 
 
@@ -38,7 +49,7 @@ def make_oracle(golden_dir, wave):
                              treynor_grid(golden_dir, 'Treynor_chan-w.rtg'),
                              treynor_grid(golden_dir, 'Treynor_chan-a.rtg'),
                              nval=treynor_grid(golden_dir, 'Treynor_chan-n.rtg'))
-    wid = {'kinematic': och.KINEMATIC, 'diffusive': och.DIFFUSIVE, 'dynamic': och.DYNAMIC}[wave]
+    wid = {'kinematic': och.KINEMATIC, 'diffusive': och.DIFFUSIVE, 'dynamic': och.DYNAMIC}[wave_of(wave)]
     return och.ChannelsOracle(b, wid, dt=CASES[wave][2], da=np.float64(900.0), slope=inp['slope'],
                               width=inp['width'], angle=inp['angle'], nval=inp['nval'],
                               outlet_ID=OUTLETS[0], n_pixels=1276)
@@ -54,7 +65,7 @@ class OracleChannels(cp.Component):
         self.ch, self.dt, self.time = ch, ch.dt, ch.time
         self.time_index, self.status = 0, 'initialized'
         self.Q_outlet = ch.Q_outlet
-        self.rows = []
+        self.rows, self.frames = [], []
 
     def update(self):
         ch = self.ch
@@ -65,6 +76,7 @@ class OracleChannels(cp.Component):
         if int(t) % 60 == 0:                                   # channels_base.py:2481-2491
             self.rows.append([float('%15.7f' % (t / 60.0))] +
                              [float('%15.7f' % np.float32(ch.Q[o])) for o in OUTLETS])
+            self.frames.append(np.float32(ch.Q))               # save_grid_dt = 60 s too
         self.time_index += 1
         self.status = 'updated'
 

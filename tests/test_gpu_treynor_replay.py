@@ -15,11 +15,12 @@ from tests.test_gpu_components import stage
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize('wave', ['kinematic', 'diffusive', 'dynamic'])
-def test_component_reproduces_shipped_hydrograph(golden_dir, tmp_path, wave):
+@pytest.mark.parametrize('case_key', ['kinematic', 'diffusive', 'diffusive_dt6', 'dynamic'])
+def test_component_reproduces_shipped_hydrograph(golden_dir, tmp_path, case_key):
+    wave = replay.wave_of(case_key)
     mod = importlib.import_module('topoflow_old_b200.components.channels_%s_wave' % wave)
     d = stage(golden_dir, 'treynor', tmp_path)
-    gold_dir, case, dt, minutes = replay.CASES[wave]
+    gold_dir, case, dt, minutes = replay.CASES[case_key]
     cfg = os.path.join(d, 'June_20_67_channels_%s_wave.cfg' % wave)
     txt = re.sub(r'^dt(\s*)\|[^|]*\|', 'dt\\1| %s |' % dt, open(cfg).read(), flags=re.M)
     open(cfg, 'w').write(txt)
@@ -50,3 +51,9 @@ def test_component_reproduces_shipped_hydrograph(golden_dir, tmp_path, wave):
     assert np.max(np.abs(a - b)) <= tol
     if wave != 'dynamic':
         assert np.mean(a == b) > 0.99                             # and almost always the same digit
+        # the grid stack the component wrote (device-side float32 frames, MSB as the RTI says)
+        gold_stack = replay.golden_stack(golden_dir, case_key)
+        mine_stack = np.fromfile(os.path.join(d, 'June_20_67_2D-Q.rts'), dtype='>f4')
+        mine_stack = mine_stack[:gold_stack.size].reshape(gold_stack.shape).astype(np.float32)
+        ulp = np.abs(mine_stack.view(np.int32).astype(np.int64) - gold_stack.view(np.int32).astype(np.int64))
+        assert ulp.max() <= 1 and np.mean(ulp == 0) > 0.99

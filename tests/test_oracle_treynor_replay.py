@@ -12,7 +12,7 @@ import pytest
 from tests import replay
 
 
-@pytest.mark.parametrize('wave', ['kinematic', 'diffusive', 'dynamic'])
+@pytest.mark.parametrize('wave', ['kinematic', 'diffusive', 'diffusive_dt6', 'dynamic'])
 def test_treynor_hydrograph_matches_reference_output(golden_dir, wave):
     gold = replay.golden_rows(golden_dir, wave)
     log = json.load(open(os.path.join(golden_dir, 'treynor', 'log_scalars.json')))[replay.CASES[wave][1]]
@@ -22,8 +22,13 @@ def test_treynor_hydrograph_matches_reference_output(golden_dir, wave):
     rows = np.array(chan.rows)[:len(gold)]
     assert rows.shape == gold.shape and gold.shape[0] >= 158
     assert np.array_equal(rows[:, 0], gold[:, 0])                      # time column
-    if wave in ('kinematic', 'diffusive'):
+    if wave != 'dynamic':
         assert np.array_equal(rows, gold)                              # every printed digit
+        # ... and every cell of every frame of the float32 grid stack, bit for bit
+        stack = replay.golden_stack(golden_dir, wave)
+        mine = np.array(chan.frames[:len(stack)])
+        assert stack.shape[0] >= 158 and mine.shape == stack.shape
+        assert np.array_equal(mine.view(np.uint32), stack.view(np.uint32))
     else:
         # dynamic wave, dt = 0.5 s, 16 800 steps: identical through the rising limb and the
         # peak; on the recession the 2017 run (macOS libm pow) and glibc drift apart by ~1e-6
