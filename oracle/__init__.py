@@ -20,8 +20,9 @@ Parity status: PINNED.
                     (oracle/coupling.py), the shipped Treynor runs Test1_kin_wave,
                     Test2_diff_wave and Test2_diff_wave_dt=6s: hydrographs digit
                     for digit, every frame of their float32 Q grid stacks
-                    (158-159 frames x 1276 cells) bit for bit, Q/u/d peaks equal
-                    to the console log to 12 digits;
+                    (158-159 frames x 1276 cells) bit for bit, Q/u/d peaks and the
+                    final report (Q_final, vol_Q, vol_R at the driver's stop)
+                    equal to the console log to its 12 printed digits;
                     Test12_dynam_wave identical through the peak, within 1e-5
                     on the recession (glibc vs the 2017 macOS libm)
 see tests/test_oracle_*.py.

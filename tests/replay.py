@@ -11,9 +11,10 @@ from oracle import coupling as cp
 from oracle import d8 as od8
 
 OUTLETS = [(34, 16), (32, 16), (37, 19), (26, 14), (30, 15)]     # June_20_67_outlets.txt (row, col)
-CASES = {'kinematic': ('out_Test1_kin_wave', 'Test1_kin_wave', 2.0, 159),
-         'diffusive': ('out_Test2_diff_wave', 'Test2_diff_wave', 2.0, 158),
-         'diffusive_dt6': ('out_Test2_diff_wave_dt6s', 'Test2_diff_wave_dt=6s', 6.0, 158),
+# fixture directory, name in log_scalars.json, channel dt [s], minute of the last golden row
+CASES = {'kinematic': ('out_Test1_kin_wave', 'Test1_kin_wave', 2.0, 158),
+         'diffusive': ('out_Test2_diff_wave', 'Test2_diff_wave', 2.0, 157),
+         'diffusive_dt6': ('out_Test2_diff_wave_dt6s', 'Test2_diff_wave_dt=6s', 6.0, 157),
          'dynamic': ('out_Test12_dynam_wave', 'Test12_dynam_wave', 0.5, 140)}
 
 
@@ -103,12 +104,24 @@ class BmiChannels(cp.Component):
         self.status = self.comp.get_status()
 
 
+def run_to_the_logged_stop(fw, channels, case, log):
+    """Carry a replay on to the update at which the reference's driver stopped
+    (topoflow_driver, dt = 6 s, n_steps in the console log): the channels
+    component has then made (6 / dt) * (n_steps - 1) + 1 updates."""
+    dt = CASES[case][2]
+    n_updates = int(round(6.0 / dt)) * (int(log['n_steps']) - 1) + 1
+    assert channels.time_index <= n_updates
+    while channels.time_index < n_updates:
+        fw.sweep()
+    return n_updates
+
+
 def run(golden_dir, channels, minutes):
     met = cp.MetSeries(60.0, rain_series(golden_dir))
     infil = cp.GreenAmptScalar(60.0, **GREEN_AMPT)
     comps = dict(met=met, chan=channels, infil=infil, snow=cp.Disabled(SM=0))
     fw = cp.Framework(comps, ['met', 'chan', 'snow', 'infil'])     # providers-file order
-    while float(channels.time) < minutes * 60 + 4:
+    while float(channels.time) < minutes * 60 + 8:            # just past the last golden row
         fw.sweep()
     return fw
 

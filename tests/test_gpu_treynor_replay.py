@@ -34,12 +34,17 @@ def test_component_reproduces_shipped_hydrograph(golden_dir, tmp_path, case_key)
     for name in ('canals__count', 'sinks__count', 'sources__count'):
         comp.set_values(name, np.array(0, dtype='int32'))
     chan = replay.BmiChannels(comp)
-    replay.run(golden_dir, chan, minutes)
+    fw = replay.run(golden_dir, chan, minutes)
     log = json.load(open(os.path.join(golden_dir, 'treynor', 'log_scalars.json')))[case]
     for name in ('Q_peak', 'u_peak', 'd_peak'):
         got = float(getattr(comp, name))
         assert abs(got - log[name]) <= 1e-10 * log[name], (name, got, log[name])
     assert float('%.12g' % float(comp.T_peak)) == log['T_peak']
+    if wave != 'dynamic':                       # the final report of the reference's run
+        replay.run_to_the_logged_stop(fw, chan, case_key, log)
+        for name, attr in (('Q_final', 'Q_outlet'), ('vol_Q', 'vol_Q'), ('vol_R', 'vol_R')):
+            got = float(getattr(comp, attr))
+            assert abs(got - log[name]) <= 1e-10 * log[name], (name, got, log[name])
     comp.finalize()
     mine = open(os.path.join(d, 'June_20_67_0D-Q.txt')).read().splitlines()
     gold = open(os.path.join(d, gold_dir, 'June_20_67_0D-Q.txt')).read().splitlines()

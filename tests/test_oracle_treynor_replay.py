@@ -18,7 +18,7 @@ def test_treynor_hydrograph_matches_reference_output(golden_dir, wave):
     log = json.load(open(os.path.join(golden_dir, 'treynor', 'log_scalars.json')))[replay.CASES[wave][1]]
     ch = replay.make_oracle(golden_dir, wave)
     chan = replay.OracleChannels(ch)
-    replay.run(golden_dir, chan, replay.CASES[wave][3])
+    fw = replay.run(golden_dir, chan, replay.CASES[wave][3])
     rows = np.array(chan.rows)[:len(gold)]
     assert rows.shape == gold.shape and gold.shape[0] >= 158
     assert np.array_equal(rows[:, 0], gold[:, 0])                      # time column
@@ -38,3 +38,9 @@ def test_treynor_hydrograph_matches_reference_output(golden_dir, wave):
     # peaks printed in 00_Full_Output.txt (12 significant digits)
     for name, attr in (('Q_peak', 'Q_peak'), ('u_peak', 'u_peak'), ('d_peak', 'd_peak'), ('T_peak', 'T_peak')):
         assert float('%.12g' % float(getattr(ch, attr))) == log[name], name
+    # the final report of the run (topoflow_driver.print_final_report): discharge at the stop,
+    # integrated discharge (update_Q_out_integral) and integrated runoff (update_R_integral)
+    if wave != 'dynamic':
+        replay.run_to_the_logged_stop(fw, chan, wave, log)
+        for name, attr in (('Q_final', 'Q_outlet'), ('vol_Q', 'vol_Q'), ('vol_R', 'vol_R')):
+            assert float('%.12g' % float(getattr(ch, attr))) == log[name], name
