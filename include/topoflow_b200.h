@@ -134,7 +134,13 @@ int tf_d8_set_codes(tf_handle h, const uint8_t* codes, const float* dx,
 /* Contributing area.  Replaces d8_component.update_area_grid
  * (d8_global.py:1018-1261).  da_rows: float64 [ny] cell area per row in m^2
  * (pixels.py:174-200); units_km != 0 divides by 1e6 first (A_units 'km^2').
- * n_unresolved_out (optional) counts flowing cells left at 0 (cycles). */
+ * n_unresolved_out (optional) counts flowing cells left at 0 (cycles).
+ * On a strip with neighbours (tf_set_strip + tf_comm_init) the call is
+ * collective: flow paths cross strips and the float32 sums must see the true
+ * child values in the reference's order, so every rank gathers the code grid
+ * of all strips over NCCL, accumulates the whole grid on its own GPU and keeps
+ * its rows (da_rows is still this strip's [ny]); the global grid must have
+ * fewer than 2^31 cells and fit one GPU (10 bytes per cell while it runs). */
 int tf_d8_area(tf_handle h, const double* da_rows, int units_km,
                int64_t* n_unresolved_out);
 

@@ -43,6 +43,11 @@ def _run_strip(rank, world, uid, wave, out_dir):
     ones = np.ones(nr, dtype=np.float32)
     stats = s.d8_build(dem[r0:r0 + nr], 30 * ones, 30 * ones, np.float32(np.sqrt(1800.0)) * ones)
     code, ds = s.d8_get(L.D8_CODE), s.d8_get(L.D8_DS)
+    # contributing area: with strips every rank gathers the code grid, accumulates the whole
+    # grid on its own GPU and keeps its rows (rows of different size: a lat/lon-like da)
+    da_rows = 900.0 * (1.0 + 0.001 * np.arange(r0, r0 + nr))
+    n_unres = s.d8_area(da_rows, units_km=True)
+    area = s.d8_get(L.D8_AREA)
     sl = lambda g: g[r0:r0 + nr].copy()
     slope = np.full((nr, NX), 0.01) + 0.001 * np.float64(sl(n))
     dt = 0.5 if wave == L.DYNAMIC else 2.0
@@ -52,6 +57,7 @@ def _run_strip(rank, world, uid, wave, out_dir):
     taps, _, bad = s.step(STEPS)
     assert bad[0] == -1 and bad[1] == -1
     out = dict(code=code, parent=s.d8_get(L.D8_PARENT_ID), inmask=s.d8_get(L.D8_INMASK),
+               area=area, n_unres=np.array([n_unres]),
                vol=s.get(L.F_VOL), d=s.get(L.F_D), u=s.get(L.F_U), Q=s.get(L.F_Q),
                stats=np.array([stats['n_flats'], stats['n_pits'], stats['n_reps']]))
     np.savez(os.path.join(out_dir, 'w%d_r%d_wave%d.npz' % (world, rank, wave)), **out)
@@ -73,8 +79,10 @@ def test_two_gpu_strips_match_single_gpu(tmp_path, wave):
     _run_strip(0, 1, None, wave, str(tmp_path))
     one = np.load(str(tmp_path / ('w1_r0_wave%d.npz' % wave)))
     parts = [np.load(str(tmp_path / ('w2_r%d_wave%d.npz' % (r, wave)))) for r in range(2)]
-    for key in ('code', 'parent', 'inmask', 'vol', 'd', 'u', 'Q'):
+    for key in ('code', 'parent', 'inmask', 'area', 'vol', 'd', 'u', 'Q'):
         got = np.concatenate([p[key] for p in parts], axis=0)
         assert np.array_equal(got, one[key]), key
+    assert one['area'].max() > 0.5 and one['area'].dtype == np.float32
+    assert parts[0]['n_unres'][0] == parts[1]['n_unres'][0] == one['n_unres'][0]
     assert one['Q'].max() > 0
     assert np.array_equal(parts[0]['stats'], one['stats'])       # all-reduced counters

@@ -126,6 +126,25 @@ int comm_allreduce_u64(tf_handle h, cudaStream_t s, unsigned long long* dev, int
     return 0;
 }
 
+// Every strip's block of rows into one tall raster that all ranks hold:
+// rank r's n_rows[r] rows of row_bytes bytes land at full + first_row[r] * row_bytes.
+int comm_allgather_rows(tf_handle h, cudaStream_t s, const void* own, void* full, size_t row_bytes,
+                        const int* first_row, const int* n_rows) {
+    TF_CHECK(h->nccl_comm != nullptr, "comm_allgather_rows: no communicator");
+    ncclComm_t comm = (ncclComm_t)h->nccl_comm;
+    TF_NCCL(g_nccl.GroupStart());
+    for (int r = 0; r < h->nranks; ++r) {
+        if (r == h->rank) continue;
+        TF_NCCL(g_nccl.Send(own, (size_t)n_rows[h->rank] * row_bytes, ncclInt8, r, comm, s));
+        TF_NCCL(g_nccl.Recv((char*)full + (size_t)first_row[r] * row_bytes, (size_t)n_rows[r] * row_bytes,
+                            ncclInt8, r, comm, s));
+    }
+    TF_NCCL(g_nccl.GroupEnd());
+    TF_CUDA(cudaMemcpyAsync((char*)full + (size_t)first_row[h->rank] * row_bytes, own,
+                            (size_t)n_rows[h->rank] * row_bytes, cudaMemcpyDeviceToDevice, s));
+    return 0;
+}
+
 int comm_free(tf_handle h) {
     if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy((ncclComm_t)h->nccl_comm);
     h->nccl_comm = nullptr;

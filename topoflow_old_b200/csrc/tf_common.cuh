@@ -199,3 +199,5 @@ int chan_derive_to_scratch(tf_handle h, int which, const double** src_out);
 int comm_exchange_rows(tf_handle h, cudaStream_t s, void* const* arrays,
                        const size_t* elem_sizes, int n_arrays);
 int comm_allreduce_u64(tf_handle h, cudaStream_t s, unsigned long long* dev, int n);
+int comm_allgather_rows(tf_handle h, cudaStream_t s, const void* own, void* full, size_t row_bytes,
+                        const int* first_row, const int* n_rows);

@@ -528,20 +528,10 @@ extern "C" int tf_d8_set_codes(tf_handle h, const uint8_t* codes, const float* d
     return d8_derive(h, false);
 }
 
-extern "C" int tf_d8_area(tf_handle h, const double* da_rows, int units_km,
-                          int64_t* n_unresolved_out) {
-    TF_TRY(use_device(h));
-    TF_CHECK(h->have_d8, "tf_d8_area: no D8 grid yet (call tf_d8_build first)");
-    TF_CHECK(da_rows != nullptr, "tf_d8_area: da_rows is NULL");
-    TF_CHECK(!h->g.has_north && !h->g.has_south,
-             "tf_d8_area: contributing area does not shard by rows; build it on one strip "
-             "holding the whole grid");
-    const Geom& g = h->g;
+// update_area_grid on one strip that holds the whole grid (da on the device)
+static int area_whole_grid(tf_handle h, const double* d_da, int units_km, int64_t* n_unresolved_out) {
     TF_TRY(raster_alloc(h, h->area, 0));
     TF_TRY(raster_alloc(h, h->pending, 0));
-    double* d_da = nullptr;
-    TF_CUDA(cudaMalloc((void**)&d_da, sizeof(double) * g.ny));
-    TF_CUDA(cudaMemcpyAsync(d_da, da_rows, sizeof(double) * g.ny, cudaMemcpyHostToDevice, h->stream));
     D8Args a = d8_args(h);
     // the area sweep addresses neighbours with "%": aprons must wrap
     TF_TRY(fill_wrap_aprons(h, h->code));
@@ -555,10 +545,95 @@ extern "C" int tf_d8_area(tf_handle h, const double* da_rows, int units_km,
     TF_CUDA(cudaMemcpyAsync(&nbad, h->counters + 8, sizeof(nbad), cudaMemcpyDeviceToHost, h->stream));
     if (!h->tb_periodic) TF_TRY(zero_aprons(h, h->code));
     TF_CUDA(cudaStreamSynchronize(h->stream));
-    cudaFree(d_da);
     if (n_unresolved_out) *n_unresolved_out = (int64_t)nbad;
     h->have_area = true;
     return 0;
+}
+
+// Strips: flow paths cross strip boundaries and the float32 sums must see the
+// true child values in the reference's order, so the area does not shard.
+// Replicas instead: every rank gathers the uint8 code grid of all
+// strips, accumulates the whole grid redundantly on its own GPU and keeps the
+// rows it owns.
+static int area_replicated(tf_handle h, const double* d_da, int units_km, int64_t* n_unresolved_out) {
+    const Geom& g = h->g;
+    TF_CHECK(h->nccl_comm != nullptr,
+             "tf_d8_area: this strip has neighbours but no communicator (tf_comm_init)");
+    TF_CHECK(h->nranks <= 64, "tf_d8_area: more than 64 strips");
+    // who owns which rows
+    unsigned long long tab[128];
+    memset(tab, 0, sizeof(tab));
+    tab[2 * h->rank] = (unsigned long long)g.row_offset;
+    tab[2 * h->rank + 1] = (unsigned long long)g.ny;
+    unsigned long long* d_tab = nullptr;
+    TF_CUDA(cudaMalloc((void**)&d_tab, sizeof(tab)));
+    TF_CUDA(cudaMemcpyAsync(d_tab, tab, sizeof(tab), cudaMemcpyHostToDevice, h->stream));
+    TF_TRY(comm_allreduce_u64(h, h->stream, d_tab, 2 * h->nranks));
+    TF_CUDA(cudaMemcpyAsync(tab, d_tab, sizeof(tab), cudaMemcpyDeviceToHost, h->stream));
+    TF_CUDA(cudaStreamSynchronize(h->stream));
+    cudaFree(d_tab);
+    int first[64], rows[64];
+    long long covered = 0;
+    for (int r = 0; r < h->nranks; ++r) {
+        first[r] = (int)tab[2 * r];
+        rows[r] = (int)tab[2 * r + 1];
+        TF_CHECK(first[r] == covered, "tf_d8_area: strips do not tile the grid (rank %d starts at row %d, "
+                 "expected %lld)", r, first[r], covered);
+        covered += rows[r];
+    }
+    TF_CHECK(covered == g.global_ny, "tf_d8_area: strips cover %lld of %d rows", covered, g.global_ny);
+    // the whole grid on this GPU
+    tf_handle T = nullptr;
+    TF_TRY(tf_create(g.nx, g.global_ny, h->device, 0, &T));
+    T->lr_periodic = h->lr_periodic;
+    T->tb_periodic = h->tb_periodic;
+    int rc = 0;
+    double* d_da_all = nullptr;
+    do {
+        if ((rc = raster_alloc(T, T->code, 0))) break;
+        if ((rc = raster_alloc(T, T->inmask, 0))) break;
+        if (cudaMalloc((void**)&d_da_all, sizeof(double) * g.global_ny) != cudaSuccess) {
+            tf_set_error("tf_d8_area: cudaMalloc failed"); rc = 1; break;
+        }
+        if (cudaStreamSynchronize(T->stream) != cudaSuccess) { tf_set_error("tf_d8_area: sync failed"); rc = 1; break; }
+        if ((rc = comm_allgather_rows(h, h->stream, h->code.p, T->code.p, (size_t)g.pitch, first, rows))) break;
+        if ((rc = comm_allgather_rows(h, h->stream, d_da, d_da_all, sizeof(double), first, rows))) break;
+        if (cudaStreamSynchronize(h->stream) != cudaSuccess) { tf_set_error("tf_d8_area: gather failed"); rc = 1; break; }
+        // aprons of the gathered code grid and its transpose, as d8_derive does for one strip
+        if (T->tb_periodic) { if ((rc = fill_wrap_aprons(T, T->code))) break; }
+        else if ((rc = zero_aprons(T, T->code))) break;
+        k_inmask<<<d8_grid(T), d8_block(), 0, T->stream>>>(d8_args(T), T->code.p, T->inmask.p);
+        T->have_d8 = true;
+        if ((rc = area_whole_grid(T, d_da_all, units_km, n_unresolved_out))) break;
+        if ((rc = raster_alloc(h, h->area, 0))) break;
+        if (cudaMemcpyAsync(h->area.p, T->area.p + (int64_t)g.row_offset * g.pitch,
+                            sizeof(float) * (size_t)g.ny * g.pitch, cudaMemcpyDeviceToDevice,
+                            h->stream) != cudaSuccess ||
+            cudaStreamSynchronize(h->stream) != cudaSuccess) {
+            tf_set_error("tf_d8_area: copying the strip's rows failed"); rc = 1; break;
+        }
+        h->have_area = true;
+    } while (0);
+    if (d_da_all) cudaFree(d_da_all);
+    std::string keep = tf_last_error();
+    tf_destroy(T);
+    if (rc) tf_set_error("%s", keep.c_str());
+    return rc;
+}
+
+extern "C" int tf_d8_area(tf_handle h, const double* da_rows, int units_km,
+                          int64_t* n_unresolved_out) {
+    TF_TRY(use_device(h));
+    TF_CHECK(h->have_d8, "tf_d8_area: no D8 grid yet (call tf_d8_build first)");
+    TF_CHECK(da_rows != nullptr, "tf_d8_area: da_rows is NULL");
+    const Geom& g = h->g;
+    double* d_da = nullptr;
+    TF_CUDA(cudaMalloc((void**)&d_da, sizeof(double) * g.ny));
+    TF_CUDA(cudaMemcpyAsync(d_da, da_rows, sizeof(double) * g.ny, cudaMemcpyHostToDevice, h->stream));
+    const int rc = (g.has_north || g.has_south) ? area_replicated(h, d_da, units_km, n_unresolved_out)
+                                                : area_whole_grid(h, d_da, units_km, n_unresolved_out);
+    cudaFree(d_da);
+    return rc;
 }
 
 extern "C" int tf_d8_get(tf_handle h, int which, void* host_out) {

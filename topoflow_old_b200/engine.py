@@ -169,7 +169,7 @@ class Strip(object):
     def set_points(self, kind, rows, cols, values):
         rows = np.ascontiguousarray(np.atleast_1d(rows), dtype=np.int32)
         cols = np.ascontiguousarray(np.atleast_1d(cols), dtype=np.int32)
-        vals = np.ascontiguousarray(np.broadcast_to(np.float64(values), rows.shape), dtype=np.float64)
+        vals = np.ascontiguousarray(np.broadcast_to(np.asarray(values, dtype=np.float64), rows.shape))
         if kind == L.PT_CANALS_IN:
             self.n_canals = rows.size
         L.check(L.lib.tf_chan_set_points(self._h, int(kind), L.ptr(rows, C.c_int32),
