@@ -24,17 +24,11 @@
 #ifndef TF_GATHER_UNROLL
 #define TF_GATHER_UNROLL 1
 #endif
-#ifndef TF_GATHER_UNROLL_DYN
-#define TF_GATHER_UNROLL_DYN 0   /* the momentum gather (3 loads per child) is faster as a loop */
-#endif
 #ifndef TF_LEAN_CHECKS
 #define TF_LEAN_CHECKS 1
 #endif
 #ifndef TF_PREFETCH
 #define TF_PREFETCH 9   /* bit 0: kfac of this tile, bit 3: look-ahead of a.pf_rows rows */
-#endif
-#ifndef TF_PROBE
-#define TF_PROBE 0      /* bit 0: skip the gather, bit 1: skip the arithmetic (timing experiments) */
 #endif
 
 struct ChanArgs {
@@ -221,10 +215,6 @@ __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int 
         apply_overbank(a, m[k], dwv[k], w[k], t[k], c[k]);
         double acc = v[k] + (R[k] * da) * dt;                  // :1334
         int mk = mask[k];
-#if TF_PROBE & 1        /* timing experiment: no inflow gather */
-        acc += (double)mk;
-        mk = 0;
-#endif
 #if TF_GATHER_UNROLL
         // the k = 1..8 adds of :1346-1361 in order, each predicated on its bit
         // of the mask; offsets are compile-time forms of the pitch, and the
@@ -251,11 +241,7 @@ __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int 
         acc -= Q[k] * dt;                                      // :1366
         acc = np_max0(acc);                                    // :1375
         v[k] = acc;
-#if TF_PROBE & 2        /* timing experiment: no depth arithmetic */
-        double dd = acc * w[k] + t[k] * ds[k];
-#else
         double dd = chan_depth(acc, w[k], t[k], ds[k]);
-#endif
         if (code[k] == 0) dd = 0.0;                            // :1511
         d[k] = np_max0(dd);                                    // :1526
     }
@@ -314,27 +300,17 @@ k_step_kinematic(const ChanArgs a) {
         else prefetch_slope_rough<PACKED>(a, j);
     }
 #endif
-#if TF_PREFETCH & 4
-    if (KF) ld4(a.kfac + i, S);
-#endif
     volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
-#if !(TF_PREFETCH & 4)
     if (KF) ld4(a.kfac + i, S);
-#endif
-    if (!KF) load_slope_rough<PACKED>(a, i, S, n);
+    else load_slope_rough<PACKED>(a, i, S, n);
     bool bad_d = false, bad_u = false;
     int bx = 0;
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
         const bool noflow = (code[k] == 0);
-#if TF_PROBE & 2        /* timing experiment: no velocity arithmetic */
-        XSection xs; xs.A_wet = d[k] + c[k]; xs.Rh = w[k];
-        double uu = xs.Rh * S[k];
-#else
-        const XSection xs = chan_xsection(d[k], w[k], t[k], c[k], noflow);
+        const XSection xs = chan_xsection_step(d[k], w[k], t[k], c[k], noflow);
         double uu = KF ? pow_two_thirds(xs.Rh) * S[k]
                        : chan_velocity<LAW>(xs.Rh, S[k], n[k], d[k]);   // kinematic: S = S_bed
-#endif
         if (noflow) uu = 0.0;                                      // :1783-1791
         u[k] = uu;
         Qn[k] = uu * xs.A_wet;                                     // :1188 of the next step

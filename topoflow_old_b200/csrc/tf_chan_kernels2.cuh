@@ -65,7 +65,9 @@ k_phase_b(const ChanArgs a) {
     for (int k = 0; k < CPT; ++k) {
         const bool noflow = (code[k] == 0);
         apply_overbank(a, ms[k] & 1, dwv[k], w[k], t[k], c[k]);
-        const XSection xs = chan_xsection(d[k], w[k], t[k], c[k], noflow);
+        // the dynamic wave needs the wetted perimeter itself (:166)
+        const XSection xs = (WAVE == 1) ? chan_xsection_step(d[k], w[k], t[k], c[k], noflow)
+                                        : chan_xsection(d[k], w[k], t[k], c[k], noflow);
         double s_free = free_slope(a, i + k, code[k], d[k], S[k], ds[k]);
         double uu;
         if (WAVE == 1) {
@@ -84,33 +86,7 @@ k_phase_b(const ChanArgs a) {
             const double dM = ((grav - fric) - Qtrm) * dt;         // :214
             double M = (u0 * v[k]) + dM;                           // :222
             int mk = mask[k];
-#if TF_GATHER_UNROLL_DYN
-            // the k = 1..8 momentum adds of :244-259 in order, each predicated on
-            // its bit of the mask; the east / west child of a pair is in registers
-            {
-                const int64_t c0 = i + k, p = a.pitch;
-#define TF_DYN_TERM(ci)                                                              \
-    {                                                                                \
-        const double uc = (a.d[ci] > 0.0) ? __ldg(a.u_old + (ci)) : 0.0;             \
-        M += (uc * __ldg(a.Q + (ci))) * dt;                                          \
-    }
-                if (mk & 1) TF_DYN_TERM(c0 + (p - 1))
-                if (mk & 2) {
-                    if (CPT == 2 && k == 1) M += (((d[0] > 0.0) ? uo[0] : 0.0) * Q[0]) * dt;
-                    else TF_DYN_TERM(c0 - 1)
-                }
-                if (mk & 4) TF_DYN_TERM(c0 - (p + 1))
-                if (mk & 8) TF_DYN_TERM(c0 - p)
-                if (mk & 16) TF_DYN_TERM(c0 - (p - 1))
-                if (mk & 32) {
-                    if (CPT == 2 && k == 0) M += (((d[1] > 0.0) ? uo[1] : 0.0) * Q[1]) * dt;
-                    else TF_DYN_TERM(c0 + 1)
-                }
-                if (mk & 64) TF_DYN_TERM(c0 + (p + 1))
-                if (mk & 128) TF_DYN_TERM(c0 + p)
-#undef TF_DYN_TERM
-            }
-#else
+            // (a loop: with three loads per child it is faster than eight predicated terms)
             while (mk) {                                           // :244-259
                 const int j = __ffs(mk) - 1;
                 mk &= mk - 1;
@@ -118,7 +94,6 @@ k_phase_b(const ChanArgs a) {
                 const double uc = (a.d[ci] > 0.0) ? __ldg(a.u_old + ci) : 0.0;
                 M += (uc * __ldg(a.Q + ci)) * dt;
             }
-#endif
             M = np_max0(M);                                        // :312
             uu = np_max0(M * vinv);                                // :318-331
         }

@@ -48,6 +48,26 @@ __device__ __forceinline__ XSection chan_xsection(double d, double w, double t, 
     return s;
 }
 
+// Wetted area and hydraulic radius for the velocity of the step kernels.
+// A_wet is the reference's expression (it becomes Q, hence vol: exact).  Rh
+// only feeds u, which is a few ulp from the reference's pow in any case:
+// A / (w + 2d/c) is evaluated as (A c) / (w c + 2d) -- one division, not two.
+#ifndef TF_RH_ONE_DIV
+#define TF_RH_ONE_DIV 1
+#endif
+__device__ __forceinline__ XSection chan_xsection_step(double d, double w, double t, double c, bool noflow) {
+#if TF_RH_ONE_DIV
+    XSection s;
+    const double L2 = d * t;
+    s.A_wet = d * (w + L2);
+    s.P_wet = 0.0;     // not used by the callers
+    s.Rh = noflow ? 0.0 : ((s.A_wet * c) / __fma_rn(w, c, 2.0 * d));
+    return s;
+#else
+    return chan_xsection(d, w, t, c, noflow);
+#endif
+}
+
 // x ** (2/3) for x >= 0 (NaN and inf pass through like pow)
 #ifndef TF_FAST_P23
 #define TF_FAST_P23 1
