@@ -304,6 +304,25 @@ def run_gpu(args):
     e2e = cells * D.world * Ke / e2e_s
     clocks = sampler.summary()
     assert bad[0] == -1 and bad[1] == -1, 'bad depth / velocity flagged: %s' % bad
+
+    # ---- the same with a rain GRID handed over every step (update_R on the device) ----
+    e2e_grid = None
+    if not args.no_grid_rain:
+        from topoflow_old_b200 import _lib as L
+        P = s.pinned_array((args.size, args.size), np.float64)
+        P[:] = RAIN_MPS
+        for k in range(1, 6):
+            s.set_forcing(k, 0.0)
+        Kg = max(2, min(K, 5))
+        D.barrier()
+        t0 = time.perf_counter()
+        for _ in range(Kg):
+            s.set_forcing(L.R_P_RAIN, P)              # 8 B/cell host -> device
+            s.assemble_R(want_sum=True)               # R and the vol_R increment, on the device
+            taps, _, bad = s.step(1)
+        D.barrier()
+        e2e_grid = cells * D.world * Kg / D.max(time.perf_counter() - t0)
+        s.set_R(RAIN_MPS, want_sum=False)
     s.timing()
 
     line = None
@@ -330,6 +349,11 @@ def run_gpu(args):
                        'parallelism': 'row strips x%d, 1 halo row of Q per step over NCCL' % D.world},
             'e2e': {'value': e2e, 'unit': 'cell-updates/s', 'h2d_bytes_per_step': 8 * 6,
                     'd2h_bytes_per_step': 8 * 4 * s.n_outlets + 16},
+            'e2e_grid_rain': None if e2e_grid is None else {
+                'value': e2e_grid, 'unit': 'cell-updates/s', 'h2d_bytes_per_step': int(8 * cells),
+                'd2h_bytes_per_step': 8 * 4 * s.n_outlets + 16 + 8,
+                'note': 'a float64 rain grid uploaded from page-locked memory every step, R and its '
+                        'integral formed on the device (tf_chan_set_forcing / tf_chan_assemble_R)'},
             'gpu_launches': int(launches),
             'clocks': clocks,
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
@@ -412,6 +436,7 @@ def main():
     ap.add_argument('--cpu-size', type=int, default=2048)
     ap.add_argument('--cpu-steps', type=int, default=25)
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--no-grid-rain', action='store_true', help='skip the extra e2e leg with a rain grid per step')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

@@ -212,14 +212,19 @@ class Strip(object):
     def frame_wait(self):
         L.check(L.lib.tf_chan_frame_wait(self._h))
 
-    def pinned_frame(self):
-        """A page-locked float32 [ny, nx] array (freed with the strip)."""
+    def pinned_array(self, shape, dtype):
+        """A page-locked host array (freed with the strip): frames, forcing grids."""
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape))
         p = C.c_void_p()
-        nbytes = 4 * self.ny * self.nx
-        L.check(L.lib.tf_host_alloc(nbytes, C.byref(p)))
+        L.check(L.lib.tf_host_alloc(n * dtype.itemsize, C.byref(p)))
         self._pinned.append(p)
-        buf = (C.c_float * (self.ny * self.nx)).from_address(p.value)
-        return np.frombuffer(buf, dtype=np.float32).reshape(self.ny, self.nx)
+        buf = (C.c_char * (n * dtype.itemsize)).from_address(p.value)
+        return np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    def pinned_frame(self):
+        """A page-locked float32 [ny, nx] array for frame()."""
+        return self.pinned_array((self.ny, self.nx), np.float32)
 
     def minmax(self):
         out = np.zeros(6, dtype=np.float64)
