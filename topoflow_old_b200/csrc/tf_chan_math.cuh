@@ -103,12 +103,28 @@ __device__ __forceinline__ double chan_velocity(double Rh, double S, double roug
     }
 }
 
+// x ** (-1/3) for x > 0, same construction as pow_two_thirds
+__device__ __forceinline__ double inv_cbrt(double x) {
+#if TF_FAST_P23
+    if (x > 1e-30 && x < 1e30) {
+        const double r = (double)rcbrtf((float)x);
+        const double h = __fma_rn(-((x * r) * r), r, 1.0);
+        return r * __fma_rn(h, __fma_rn(h, 2.0 / 9.0, 1.0 / 3.0), 1.0);
+    }
+#endif
+    return 1.0 / cbrt(x);
+}
+
 // update_friction_factor :1654-1721
 template <int LAW>
 __device__ __forceinline__ double chan_friction(double d, double rough) {
     if (!(d > 0.0)) return 0.0;
     if (LAW == 0) {
+#if TF_FAST_P23
+        return TF_G * ((rough * rough) * inv_cbrt(d));      // g n^2 / d^(1/3), a few ulp
+#else
         return TF_G * ((rough * rough) / cbrt(d));
+#endif
     } else {
         double sm = (TF_AVAL / rough) * d;
         sm = np_maxv(sm, 1.1);
