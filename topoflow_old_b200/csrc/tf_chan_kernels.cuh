@@ -1,16 +1,23 @@
 // tf_chan_kernels.cuh -- the routing kernels.
 //
-// Thread layout: a warp owns 128 consecutive cells of one row, 4 per lane, so
-// every raster access is a 128-bit (float64 / float32) or 32-bit (uint8) load
-// per lane and fully coalesced per warp.  A block is 32 x 8 threads = a tile
-// of 128 columns x 8 rows; vertical neighbours are mostly served by the
-// block's own L1 lines, the rest by L2.
+// Thread layout: a warp owns 64 consecutive cells of one row, TF_CPT = 2 per
+// lane, so every raster access is a 128-bit (float64), 64-bit (float32) or
+// 16-bit (uint8) load per lane and fully coalesced per warp.  A block is
+// 32 x 8 threads = a tile of 64 columns x 8 rows, 4 blocks per SM at 64
+// registers; vertical neighbours are mostly served by the block's own L1
+// lines, the rest by L2.
 //
 // The eight-neighbour inflow uses the per-cell child mask built with the D8
 // grid (tf_d8.cu:k_inmask): bit j set means "the neighbour opposite to
-// direction j drains into me", and bits are visited in ascending j, which is
-// the reference's k = 1..8 order (channels_base.py:1346-1361).  The running
-// sum stays in registers.
+// direction j drains into me"; the adds are made in ascending j, which is the
+// reference's k = 1..8 order (channels_base.py:1346-1361), each predicated on
+// its bit.  The running sum stays in registers.
+//
+// Latency: a tile's loads form dependent chains (mask -> neighbour Q, angle
+// index -> table, depth -> velocity factor).  Every block therefore asks L2
+// (prefetch.global.L2, no registers held) for the cells of the tile one tile
+// row further south, which a later wave of blocks will read: their loads are
+// L2 hits instead of DRAM round trips (ChanArgs::pf_rows, TF_B200_PF_ROWS).
 #pragma once
 #include "tf_chan_math.cuh"
 
@@ -184,7 +191,7 @@ __device__ __forceinline__ void flag_bad(const ChanArgs& a, int which, int x, in
 }
 
 // ---------------------------------------------------------------------------
-// mass balance + trapezoid depth for 4 cells (update_flow_volume :1308-1375,
+// mass balance + trapezoid depth for CPT cells (update_flow_volume :1308-1375,
 // update_flow_depth :1379-1532).  Returns the effective shape in w, t, c.
 // ---------------------------------------------------------------------------
 template <bool PACKED>
