@@ -76,6 +76,38 @@ def log_scalars(path):
     return out
 
 
+def bmi_tables():
+    """The introspection tables of the reference's channels components, read
+    out of its source as literals (the files are Python 2 and cannot be
+    imported): what get_input_var_names / get_var_name / get_var_units /
+    get_attribute must answer."""
+    import ast
+    comp = '/root/reference/topoflow/components/'
+
+    def literal(path, name):
+        lines = open(comp + path).read().splitlines()
+        start = next(i for i, l in enumerate(lines) if l.startswith('    %s = ' % name))
+        body, depth = '', 0
+        for l in lines[start:]:
+            l = l.split('#')[0]
+            if not body:
+                l = l.split('=', 1)[1]
+            body += l + '\n'
+            depth += l.count('[') + l.count('{') - l.count(']') - l.count('}')
+            if depth == 0 and body.strip():
+                break
+        return ast.literal_eval(body.strip())
+
+    out = {'input_var_names': literal('channels_base.py', '_input_var_names'),
+           'output_var_names': literal('channels_base.py', '_output_var_names'),
+           'var_name_map': literal('channels_base.py', '_var_name_map'),
+           'var_units_map': literal('channels_base.py', '_var_units_map'),
+           'att_map': {w: literal('channels_%s_wave.py' % w, '_att_map')
+                       for w in ('kinematic', 'diffusive', 'dynamic')},
+           'd8_att_map': literal('d8_global.py', '_att_map')}
+    return out
+
+
 def main():
     t = os.path.join(REF, 'Treynor_Iowa_30m')
     for f in TREYNOR_IN:
@@ -89,6 +121,7 @@ def main():
                                               '00_Full_Output.txt'))
     json.dump(scal, open(os.path.join(HERE, 'treynor', 'log_scalars.json'), 'w'),
               indent=1, sort_keys=True)
+    json.dump(bmi_tables(), open(os.path.join(HERE, 'bmi_tables.json'), 'w'), indent=1, sort_keys=True)
     p = os.path.join(REF, 'Test_Plane_Canal')
     for f in PLANE_IN:
         cp(os.path.join(p, f), os.path.join(HERE, 'plane_canal', f))

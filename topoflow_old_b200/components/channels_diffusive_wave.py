@@ -14,7 +14,8 @@ class channels_component(channels_base.channels_component):
         'comp_name': 'ChannelsDiffWave', 'model_family': 'TopoFlow',
         'cfg_template_file': 'Channels_Diffusive_Wave.cfg.in',
         'cfg_extension': '_channels_diffusive_wave.cfg',
-        'cmt_var_prefix': '/ChannelsDiffWave/Input/Var/', 'gui_xml_file': '',
+        'cmt_var_prefix': '/ChannelsDiffWave/Input/Var/',
+        'gui_xml_file': '/home/csdms/cca/topoflow/3.1/src/share/cmt/gui/Channels_Diffusive_Wave.xml',
         'dialog_title': 'Channels: Diffusive Wave Parameters', 'time_units': 'seconds'}
 
     def get_component_name(self):

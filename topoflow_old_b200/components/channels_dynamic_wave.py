@@ -14,7 +14,8 @@ class channels_component(channels_base.channels_component):
         'comp_name': 'ChannelsDynamWave', 'model_family': 'TopoFlow',
         'cfg_template_file': 'Channels_Dynamic_Wave.cfg.in',
         'cfg_extension': '_channels_dynamic_wave.cfg',
-        'cmt_var_prefix': '/ChannelsDynamWave/Input/Var/', 'gui_xml_file': '',
+        'cmt_var_prefix': '/ChannelsDynamWave/Input/Var/',
+        'gui_xml_file': '/home/csdms/cca/topoflow/3.1/src/share/cmt/gui/Channels_Dynamic_Wave.xml',
         'dialog_title': 'Channels: Dynamic Wave Parameters', 'time_units': 'seconds'}
 
     def get_component_name(self):

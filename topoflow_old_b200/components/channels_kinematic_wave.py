@@ -14,7 +14,8 @@ class channels_component(channels_base.channels_component):
         'comp_name': 'ChannelsKinWave', 'model_family': 'TopoFlow',
         'cfg_template_file': 'Channels_Kinematic_Wave.cfg.in',
         'cfg_extension': '_channels_kinematic_wave.cfg',
-        'cmt_var_prefix': '/ChannelsKinWave/Input/Var/', 'gui_xml_file': '',
+        'cmt_var_prefix': '/ChannelsKinWave/Input/Var/',
+        'gui_xml_file': '/home/csdms/cca/topoflow/3.1/src/share/cmt/gui/Channels_Kinematic_Wave.xml',
         'dialog_title': 'Channels: Kinematic Wave Parameters', 'time_units': 'seconds'}
 
     def get_component_name(self):

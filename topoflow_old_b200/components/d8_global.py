@@ -23,7 +23,9 @@ class d8_component(d8_base.d8_component):
         'grid_type': 'uniform', 'time_step_type': 'fixed', 'step_method': 'explicit',
         'comp_name': 'D8Global', 'model_family': 'TopoFlow',
         'cfg_template_file': 'd8_global.cfg.in', 'cfg_extension': '_d8_global.cfg',
-        'cmt_var_prefix': '/D8Global/Input/Var/', 'gui_xml_file': '',
+        'cmt_var_prefix': '/D8Global/Input/Var/',
+        # (the reference's d8_global does name the channels dialog here, d8_global.py:74)
+        'gui_xml_file': '/home/csdms/cca/topoflow/3.1/src/share/cmt/gui/Channels_Kinematic_Wave.xml',
         'dialog_title': 'D8 Global Parameters', 'time_units': 'seconds'}
 
     def get_component_name(self):
