@@ -154,16 +154,21 @@ class ChannelsOracle(object):
         self.S_bed = self.slope
 
     def set_sources(self, rows, cols, Q):
+        """source_IDs / sources_Q as initialize_diversion_vars builds them from the
+        diversions component's x, y (channels_base.py:1018-1023)."""
         self.n_sources = len(rows)
         self.source_IDs = (np.int32(rows), np.int32(cols))
         self.sources_Q = np.float64(Q)
 
     def set_sinks(self, rows, cols, Q):
+        """channels_base.py:1024-1029."""
         self.n_sinks = len(rows)
         self.sink_IDs = (np.int32(rows), np.int32(cols))
         self.sinks_Q = np.float64(Q)
 
     def set_canals(self, in_rows, in_cols, out_rows, out_cols, fraction, out_Q):
+        """channels_base.py:1030-1044; canals_out_Q is the diversions component's
+        own array (diversions_fraction_method.py:545, updated in place :701-704)."""
         self.n_canals = len(in_rows)
         self.canal_in_IDs = (np.int32(in_rows), np.int32(in_cols))
         self.canal_out_IDs = (np.int32(out_rows), np.int32(out_cols))

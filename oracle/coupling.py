@@ -19,6 +19,7 @@ import numpy as np
 
 
 def scalar(x, dtype='float64'):
+    """A mutable 0-d array, BMI_base.initialize_scalar (utils/BMI_base.py:1941-1972)."""
     return np.array(x, dtype=dtype)
 
 
@@ -28,7 +29,7 @@ class TimeInterpData(object):
     variable the provider updates IN PLACE shows its new value in v1 after the
     first update(), while a variable the provider REBINDS keeps its old one."""
 
-    def __init__(self, v1, t1):
+    def __init__(self, v1, t1):                                 # time_interpolation.py:63-89
         self.v2 = v1
         self.t2 = t1
         self.v1 = v1.copy()
@@ -36,7 +37,7 @@ class TimeInterpData(object):
         self.a = np.float64(0)
         self.b = v1
 
-    def update(self, v2, t2):
+    def update(self, v2, t2):                                   # time_interpolation.py:91-133
         self.t1 = self.t2.copy()
         try:
             self.v1[:] = self.v2.copy()
@@ -55,7 +56,7 @@ class TimeInterpData(object):
             self.a = np.float64(0)
             self.b = v2
 
-    def value_at(self, time):
+    def value_at(self, time):                                   # time_interpolation.py:574-685
         return (self.a * time) + self.b
 
 
@@ -65,12 +66,12 @@ class Component(object):
     provides = ()          # attribute names other components read
     uses = ()              # (attribute, provider component name, provider attribute)
 
-    def __init__(self, dt):
+    def __init__(self, dt):                                     # BMI_base.py:1007-1063
         self.dt = scalar(dt)
         self.time = scalar(0)
         self.time_index = 0
 
-    def advance(self):
+    def advance(self):                                          # update_time, BMI_base.py:1067-1114
         self.time_index += 1
         self.time += self.dt
         self.status = 'updated'
@@ -78,7 +79,8 @@ class Component(object):
 
 class Disabled(Component):
     """A provider switched off in its cfg file: hands out 0-d zeros that never
-    change, never advances its clock (its update() returns at once)."""
+    change, never advances its clock (its update() returns at once; e.g.
+    snow_base.py:193, diversions_base.py:100-126, infil_base.py:223)."""
 
     def __init__(self, **values):
         Component.__init__(self, 1.0)
@@ -130,7 +132,7 @@ class MetGrid(Component):
         self.P_rain = np.zeros_like(P)
         self.rho_H2O = scalar(rho_H2O)
 
-    def update(self):
+    def update(self):                                           # met_base.py:650-700, :1037-1038
         self.P_rain[:] = self.P                                 # T_air > 0
         self.advance()
 
@@ -195,7 +197,7 @@ class GreenAmptScalar(Component):
 class Framework(object):
     """emeli.py run_model with time_interp_method = 'Linear'."""
 
-    def __init__(self, comps, order):
+    def __init__(self, comps, order):       # emeli.py:1736-1828, time_interpolation.py:190-293
         self.comps = comps                  # name -> component
         self.order = order                  # provider file order
         self.time = np.float64(0)
