@@ -78,13 +78,17 @@ enum tf_points { TF_PT_SOURCES = 0, TF_PT_SINKS = 1, TF_PT_CANALS_IN = 2,
 
 /* ---- lifetime ------------------------------------------------------------ */
 
-/* Last error message of the calling thread ("" if none). */
+/* Last error message of the calling thread ("" if none).  The reference prints
+ * and raises (channels_base.py:2028, :2078; outlets.py:81); the Python layer
+ * turns this text into the same exceptions. */
 const char* tf_last_error(void);
 
-/* Library/build identification, e.g. "topoflow_b200 0.1 sm_100a". */
+/* Library/build identification, e.g. "topoflow_b200 0.1 sm_100a" (the
+ * reference's get_attribute('version'), channels_kinematic_wave.py:42). */
 const char* tf_version(void);
 
-/* Number of CUDA devices visible, or -1 on error (no compute is started). */
+/* Number of CUDA devices visible, or -1 on error (no compute is started).
+ * No counterpart in the reference (CPU only). */
 int tf_device_count(void);
 
 /* Create a strip of ny rows x nx columns on CUDA device `device`.
@@ -103,7 +107,8 @@ int tf_set_strip(tf_handle h, int row_offset, int global_ny, int has_north,
 /* Free every device buffer of the handle (channels_base.py:708-722 finalize). */
 int tf_destroy(tf_handle h);
 
-/* Block until all work queued on the handle has finished. */
+/* Block until all work queued on the handle has finished.  No counterpart in
+ * the reference (every NumPy call is synchronous). */
 int tf_sync(tf_handle h);
 
 /* ---- D8 grid builder ------------------------------------------------------ */
@@ -144,7 +149,9 @@ int tf_d8_set_codes(tf_handle h, const uint8_t* codes, const float* dx,
 int tf_d8_area(tf_handle h, const double* da_rows, int units_km,
                int64_t* n_unresolved_out);
 
-/* Copy one D8 product to a dense host grid of the field's element type. */
+/* Copy one D8 product to a dense host grid of the field's element type: the
+ * attributes other components read from the embedded d8 object (d8_grid,
+ * parent_ID_grid, ds, dw, A; d8_base.py:119-123, channels_base.py:756-793). */
 int tf_d8_get(tf_handle h, int which, void* host_out);
 
 /* ---- channel routing ------------------------------------------------------ */
@@ -218,7 +225,8 @@ int tf_chan_step(tf_handle h, int n_steps, double* taps_out,
                  double* canals_in_out, int64_t* bad_out);
 
 /* Same work, nothing copied back: queue n_steps on the handle's stream and
- * return.  Used to time the kernels with inputs resident in HBM. */
+ * return.  Used to time the kernels with inputs resident in HBM.  No counterpart
+ * in the reference. */
 int tf_chan_step_async(tf_handle h, int n_steps);
 
 /* Copy one grid (enum tf_field) to a dense float64 host grid.  Derived fields
@@ -245,11 +253,15 @@ int tf_chan_minmax(tf_handle h, double* out6);
 int tf_chan_frame(tf_handle h, int which, int swap_endian, float* host_out, int async);
 int tf_chan_frame_wait(tf_handle h);
 
-/* Page-locked host memory for frames and forcing grids (cudaHostAlloc). */
+/* Page-locked host memory for frames and forcing grids (cudaHostAlloc).  No
+ * counterpart in the reference; it replaces the NumPy buffers of
+ * rts_file.add_grid (utils/rts_files.py:313-396) on the caller's side. */
 int tf_host_alloc(size_t bytes, void** out);
 int tf_host_free(void* p);
 
-/* Device-side timing of everything queued by tf_chan_step* since the last
+/* (No counterpart in the reference beyond the cProfile notes in its comments,
+ * channels_base.py:1398-1400.)
+ * Device-side timing of everything queued by tf_chan_step* since the last
  * call: out[0] = elapsed ms (CUDA events on the handle's stream), out[1] =
  * steps, out[2] = kernel launches, out[3] = bytes per cell-update actually
  * addressed by the step kernels for the current layout. */
@@ -281,7 +293,8 @@ int tf_sum_R_noalloc(const double* R_dev, int nx, int ny, long long pitch,
 
 /* ---- row-strip decomposition over several GPUs ---------------------------- */
 
-/* 128-byte NCCL unique id for tf_comm_init (rank 0 creates, all ranks use). */
+/* 128-byte NCCL unique id for tf_comm_init (rank 0 creates, all ranks use).
+ * The reference is a single process: nothing in it corresponds to tf_comm_*. */
 int tf_comm_unique_id(uint8_t* id128);
 
 /* Join a communicator of `nranks` strips stacked north to south; rank r's
