@@ -364,7 +364,7 @@ def run_gpu(args):
                          'kernel_ms': kernel_ms},
             'wall_ms_timed_region': wall_ms,
         }
-        if not args.no_cpu:
+        if not args.no_cpu and D.world == 1:          # the CPU baseline is an N = 1 item
             v, el = cpu_path(args.wave, args.cpu_size, args.cpu_steps, 2)
             line['cpu_baseline'] = {'value': v, 'unit': 'cell-updates/s', 'cores': 1, 'kind': 'port',
                                     'sample': '%d steps of the same workload on a %dx%d grid (%.1f s), '
@@ -372,6 +372,8 @@ def run_gpu(args):
                                                   args.cpu_steps, args.cpu_size, args.cpu_size, el,
                                                   sys.version_info[0], sys.version_info[1],
                                                   'found' if _have_py27() else 'unavailable on this box')}
+        elif D.world > 1:
+            line['cpu_baseline'] = None               # measured at N = 1 only
     s.close()
     D.close()
     if line is not None:
