@@ -280,7 +280,7 @@ int chan_free(tf_handle h) {
     raster_free(h->vol); raster_free(h->d); raster_free(h->u); raster_free(h->u2);
     raster_free(h->Qa); raster_free(h->Qb); raster_free(h->R);
     for (int k = 0; k < TF_R_COUNT; ++k) { raster_free(h->forc[k]); h->forc_is_grid[k] = false; }
-    raster_free(h->f); raster_free(h->mstate);
+    raster_free(h->mstate);
     raster_free(h->w64); raster_free(h->tan64); raster_free(h->cos64);
     raster_free(h->S64); raster_free(h->n64); raster_free(h->ds64); raster_free(h->kfac);
     raster_free(h->w32); raster_free(h->S32); raster_free(h->n32); raster_free(h->ds32);

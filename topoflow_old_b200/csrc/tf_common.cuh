@@ -134,7 +134,7 @@ struct tf_handle_s {
     double* da_rows = nullptr;            // device [ny + 2] (index y + 1)
     bool chan_ready = false;
     // state
-    Raster<double> vol, d, u, u2, Qa, Qb, R, f;
+    Raster<double> vol, d, u, u2, Qa, Qb, R;
     double *Qcur = nullptr, *Qnext = nullptr;   // -> Qa.p / Qb.p
     double *ucur = nullptr, *unext = nullptr;   // dynamic wave double buffer
     bool R_is_grid = false;
