@@ -119,8 +119,6 @@ extern "C" int tf_create(int nx, int ny, int device, unsigned flags,
     cudaDeviceGetStreamPriorityRange(&lo, &hi);
     cudaError_t e = cudaStreamCreateWithPriority(&h->stream, cudaStreamNonBlocking, lo);
     if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&h->stream_edge, cudaStreamNonBlocking, hi);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_a, cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_b, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_edge, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreate(&h->t0);
@@ -165,8 +163,6 @@ extern "C" int tf_destroy(tf_handle h) {
     if (h->bad) cudaFree(h->bad);
     if (h->t0) cudaEventDestroy(h->t0);
     if (h->t1) cudaEventDestroy(h->t1);
-    if (h->ev_a) cudaEventDestroy(h->ev_a);
-    if (h->ev_b) cudaEventDestroy(h->ev_b);
     if (h->ev_edge) cudaEventDestroy(h->ev_edge);
     if (h->ev_main) cudaEventDestroy(h->ev_main);
     if (h->stream) cudaStreamDestroy(h->stream);

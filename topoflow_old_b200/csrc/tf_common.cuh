@@ -108,7 +108,7 @@ struct tf_handle_s {
     Geom g{};
     cudaStream_t stream = nullptr;        // main stream
     cudaStream_t stream_edge = nullptr;   // boundary rows + halo exchange
-    cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_edge = nullptr, ev_main = nullptr;
+    cudaEvent_t ev_edge = nullptr, ev_main = nullptr;
 
     // ---- D8 -------------------------------------------------------------
     Raster<float> dem;            // DEM, float32
