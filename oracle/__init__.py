@@ -23,7 +23,9 @@ Parity status: PINNED.
                     (158-159 frames x 1276 cells) bit for bit, Q/u/d peaks and the
                     final report (Q_final, vol_Q, vol_R at the driver's stop)
                     equal to the console log to its 12 printed digits;
-                    Test12_dynam_wave identical through the peak, within 1e-5
+                    Test8_snow_degree_day (snowmelt as a second source, through
+                    EMELI's interpolation of a rebound scalar) likewise, with
+                    vol_SM; Test12_dynam_wave identical through the peak, within 1e-5
                     on the recession (glibc vs the 2017 macOS libm)
 see tests/test_oracle_*.py.
 """

@@ -94,7 +94,7 @@ class Disabled(Component):
 
 class MetSeries(Component):
     """Rain from a one-value-per-line text series [mm/h], dt seconds apart."""
-    provides = ('P_rain', 'rho_H2O')
+    provides = ('P_rain', 'P_snow', 'T_air', 'rho_H2O')
     MMPH_TO_MPS = np.float64(1) / np.float64(3600000)          # met_base.py:559
 
     def __init__(self, dt, series_mmph, T_air=20.0, rho_H2O=1000.0):
@@ -103,6 +103,7 @@ class MetSeries(Component):
         self.next = 0
         self.P = scalar(0)
         self.P_rain = scalar(0)                                 # :608
+        self.P_snow = scalar(0)
         self.T_air = scalar(T_air)
         self.rho_H2O = scalar(rho_H2O)
         self.read_input_files()                                 # :626
@@ -117,6 +118,7 @@ class MetSeries(Component):
 
     def update(self):                                           # :650-700
         self.P_rain[()] = self.P * (self.T_air > 0)             # :1037-1038, in place
+        self.P_snow[()] = self.P * (self.T_air <= 0)            # update_P_snow, in place
         if self.time_index > 0:
             self.read_input_files()
         self.advance()
@@ -165,6 +167,39 @@ class CanalDiversions(Component):
         for k in range(int(self.n_canals)):
             self.canals_out_Q[k] = self.canal_Q[k, int(self.nt_canals[k]) - 1]
         self.canal_Q = np.roll(self.canal_Q, 1, axis=1)
+        self.advance()
+
+
+class SnowDegreeDayScalar(Component):
+    """snow_degree_day with every input a scalar: the potential meltrate
+    (snow_degree_day.py:272-312), capped by the snow that is there
+    (snow_base.py:365-380), then the water-equivalent and depth bookkeeping
+    (:397-440).  self.SM is REBOUND at every update, like the reference."""
+    provides = ('SM',)
+    uses = (('T_air', 'met', 'T_air'), ('P_snow', 'met', 'P_snow'), ('rho_H2O', 'met', 'rho_H2O'))
+
+    def __init__(self, dt, c0, T0, h0_snow, h0_swe, rho_snow, da, n_pixels):
+        Component.__init__(self, dt)
+        self.c0, self.T0, self.rho_snow = np.float64(c0), np.float64(T0), np.float64(rho_snow)
+        self.da, self.n_pixels = np.float64(da), n_pixels
+        self.SM = scalar(0)                                     # snow_base.py:323-325
+        self.h_snow, self.h_swe = scalar(h0_snow), scalar(h0_swe)
+        self.vol_SM = scalar(0)
+        self.T_air, self.P_snow, self.rho_H2O = scalar(0), scalar(0), scalar(1000.0)
+
+    def update(self):                                           # snow_base.py:176-233
+        M = (self.c0 / np.float64(8.64E7)) * (self.T_air - self.T0)       # [m/s]
+        self.SM = np.maximum(M, np.float64(0))
+        density_ratio = (self.rho_H2O / self.rho_snow)
+        SM_max = (density_ratio / self.dt) * self.h_snow
+        self.SM = np.minimum(self.SM, SM_max)
+        self.SM = np.maximum(self.SM, np.float64(0))
+        volume = np.float64(self.SM * self.da * self.dt)        # update_SM_integral :384-393
+        self.vol_SM += (volume * self.n_pixels)
+        self.h_swe += (self.P_snow * self.dt)                   # update_swe :419-428
+        self.h_swe -= (self.SM * self.dt)
+        np.maximum(self.h_swe, np.float64(0), self.h_swe)
+        self.h_snow = self.h_swe * density_ratio                # update_depth :432-440
         self.advance()
 
 

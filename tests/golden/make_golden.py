@@ -23,11 +23,13 @@ TREYNOR_IN = ['Treynor.rti', 'Treynor_DEM.rtg', 'Treynor_flow.rtg',
               'June_20_67_channels_dynamic_wave.cfg',
               'June_20_67_d8_global.cfg', 'June_20_67_path_info.cfg',
               'June_20_67_outlets.txt', 'June_20_67_rain_rates.txt',
-              'June_20_67_meteorology.cfg', 'June_20_67_infil_green_ampt.cfg']
+              'June_20_67_meteorology.cfg', 'June_20_67_infil_green_ampt.cfg',
+              'June_20_67_snow_degree_day.cfg']
 TREYNOR_OUT = {'Test1_kin_wave': ['June_20_67_0D-Q.txt', 'June_20_67_2D-Q.rti', 'June_20_67_2D-Q.rts'],
                'Test2_diff_wave': ['June_20_67_0D-Q.txt', 'June_20_67_2D-Q.rts'],
                'Test2_diff_wave_dt=6s': ['June_20_67_0D-Q.txt', 'June_20_67_2D-Q.rts'],
-               'Test12_dynam_wave': ['June_20_67_0D-Q.txt']}
+               'Test12_dynam_wave': ['June_20_67_0D-Q.txt'],
+               'Test8_snow_degree_day': ['June_20_67_0D-Q.txt']}
 PLANE_IN = ['plane.rti', 'plane_DEM.rtg', 'plane_slope.rtg', 'plane_flow.rtg',
             'plane_chan-a.rtg', 'plane_chan-n.rtg', 'plane_chan-w.rtg',
             'Rain_100mmph_on_right.rtg', 'Rain_100mmph_on_right.rti',
@@ -67,6 +69,7 @@ def log_scalars(path):
             'vol_IN': r'vol_IN\s+\(infiltration\):\s+([0-9.eE+-]+)',
             'vol_Q': r'vol_Q\s+\(discharge\):\s+([0-9.eE+-]+)',
             'vol_R': r'vol_R\s+\(runoff\):\s+([0-9.eE+-]+)',
+            'vol_SM': r'vol_SM\s+\(snowmelt\):\s+([0-9.eE+-]+)',
             'n_steps': r'Number of timesteps:\s+(\d+)'}
     out = {}
     for k, pat in pats.items():

@@ -15,7 +15,9 @@ OUTLETS = [(34, 16), (32, 16), (37, 19), (26, 14), (30, 15)]     # June_20_67_ou
 CASES = {'kinematic': ('out_Test1_kin_wave', 'Test1_kin_wave', 2.0, 158),
          'diffusive': ('out_Test2_diff_wave', 'Test2_diff_wave', 2.0, 157),
          'diffusive_dt6': ('out_Test2_diff_wave_dt6s', 'Test2_diff_wave_dt=6s', 6.0, 157),
-         'dynamic': ('out_Test12_dynam_wave', 'Test12_dynam_wave', 0.5, 140)}
+         'dynamic': ('out_Test12_dynam_wave', 'Test12_dynam_wave', 0.5, 140),
+         # kinematic wave + snow_degree_day as the snow provider (everything else as Test1)
+         'kinematic_snow': ('out_Test8_snow_degree_day', 'Test8_snow_degree_day', 2.0, 158)}
 
 
 def wave_of(case):
@@ -116,10 +118,28 @@ def run_to_the_logged_stop(fw, channels, case, log):
     return n_updates
 
 
-def run(golden_dir, channels, minutes):
+def cfg_values(path):
+    """name -> float for the numeric records of a TopoFlow cfg file."""
+    out = {}
+    for line in open(path):
+        f = [x.strip() for x in line.split('|')]
+        if len(f) == 4 and f[2] in ('float', 'double', 'long', 'int'):
+            out[f[0]] = float(f[1])
+    return out
+
+
+def degree_day_snow(golden_dir):
+    """The snow provider of Test8 (June_20_67_snow_degree_day.cfg; the shipped run only flips
+    its comp_status to Enabled)."""
+    v = cfg_values(os.path.join(golden_dir, 'treynor', 'June_20_67_snow_degree_day.cfg'))
+    return cp.SnowDegreeDayScalar(v['dt'], c0=v['c0'], T0=v['T0'], h0_snow=v['h0_snow'],
+                                  h0_swe=v['h0_swe'], rho_snow=v['rho_snow'], da=900.0, n_pixels=1276)
+
+
+def run(golden_dir, channels, minutes, snow=None):
     met = cp.MetSeries(60.0, rain_series(golden_dir))
     infil = cp.GreenAmptScalar(60.0, **GREEN_AMPT)
-    comps = dict(met=met, chan=channels, infil=infil, snow=cp.Disabled(SM=0))
+    comps = dict(met=met, chan=channels, infil=infil, snow=snow or cp.Disabled(SM=0))
     fw = cp.Framework(comps, ['met', 'chan', 'snow', 'infil'])     # providers-file order
     while float(channels.time) < minutes * 60 + 8:            # just past the last golden row
         fw.sweep()

@@ -44,3 +44,26 @@ def test_treynor_hydrograph_matches_reference_output(golden_dir, wave):
         replay.run_to_the_logged_stop(fw, chan, wave, log)
         for name, attr in (('Q_final', 'Q_outlet'), ('vol_Q', 'vol_Q'), ('vol_R', 'vol_R')):
             assert float('%.12g' % float(getattr(ch, attr))) == log[name], name
+
+
+def test_treynor_with_degree_day_snow_matches_reference_output(golden_dir):
+    """Test8_snow_degree_day: the same run with snowmelt as a second source of
+    runoff.  SM reaches the channels through EMELI's linear interpolation of a
+    REBOUND 0-d array (a ramp over the snow component's first hour), so this
+    pins the coupling restatement as well as the provider."""
+    case = 'kinematic_snow'
+    gold = replay.golden_rows(golden_dir, case)
+    log = json.load(open(os.path.join(golden_dir, 'treynor', 'log_scalars.json')))[replay.CASES[case][1]]
+    ch = replay.make_oracle(golden_dir, case)
+    chan = replay.OracleChannels(ch)
+    snow = replay.degree_day_snow(golden_dir)
+    fw = replay.run(golden_dir, chan, replay.CASES[case][3], snow=snow)
+    rows = np.array(chan.rows)[:len(gold)]
+    assert gold.shape == (159, 6) and np.array_equal(rows, gold)
+    assert gold[1, 1] > 0                      # melt water reaches the outlet before any rain does
+    for name in ('Q_peak', 'u_peak', 'd_peak', 'T_peak'):
+        assert float('%.12g' % float(getattr(ch, name))) == log[name], name
+    replay.run_to_the_logged_stop(fw, chan, case, log)
+    for name, attr in (('Q_final', 'Q_outlet'), ('vol_Q', 'vol_Q'), ('vol_R', 'vol_R')):
+        assert float('%.12g' % float(getattr(ch, attr))) == log[name], name
+    assert float('%.10g' % float(snow.vol_SM)) == log['vol_SM']
