@@ -129,6 +129,15 @@ int tf_d8_build(tf_handle h, const float* dem, const float* dx,
                 int link_flats, int lr_periodic, int tb_periodic,
                 int64_t* stats_out);
 
+/* Pixel sizes of row 0 of the GLOBAL grid.  start_new_d8_codes divides every
+ * row's elevation drops by the distances of row 0 (d8_global.py:209-211), so a
+ * strip that does not hold global row 0 must not use its own first row's on a
+ * grid whose dx varies by row (geographic pixels, pixels.py:72-173).  Optional:
+ * without this call a strip inside a communicator takes rank 0's values over
+ * NCCL in tf_d8_build; a strip with neither uses its own dx[0], dy[0], dd[0]
+ * (right for the whole grid and for fixed-length pixels). */
+int tf_d8_set_row0_sizes(tf_handle h, float dx0, float dy0, float dd0);
+
 /* Install a ready-made uint8 D8 code grid instead of deriving it from a DEM
  * (what the pre-3.5 tf_d8_base did with <site>_flow.rtg; d8_global.py:162-166).
  * Derives parent IDs, ds, dw and the child mask exactly as tf_d8_build. */

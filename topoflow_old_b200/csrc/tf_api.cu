@@ -105,8 +105,8 @@ extern "C" int tf_create(int nx, int ny, int device, unsigned flags,
     g.nx = nx;
     g.ny = ny;
     g.pitch = round_up(nx, 32);
-    g.n_alloc = (int64_t)(ny + 2) * g.pitch + 2 * TF_GUARD;
-    g.origin = TF_GUARD + g.pitch;
+    g.n_alloc = (int64_t)(ny + 2 * TF_APRON) * g.pitch + 2 * TF_GUARD;
+    g.origin = TF_GUARD + (int64_t)TF_APRON * g.pitch;
     g.row_offset = 0;
     g.global_ny = ny;
     g.has_north = g.has_south = 0;

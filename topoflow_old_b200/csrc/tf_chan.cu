@@ -47,12 +47,15 @@ extern "C" int tf_chan_init(tf_handle h, int wave, int law, double dt, const dou
     h->mut_width = h->hp[TF_P_WIDTH].is_grid;
     h->mut_angle = h->hp[TF_P_TAN_ANGLE].is_grid;
     // cell areas per row, with apron slots
-    if (!h->da_rows) TF_CUDA(cudaMalloc((void**)&h->da_rows, sizeof(double) * (g.ny + 2)));
+    const int n_da = g.ny + 2 * TF_APRON;
+    if (!h->da_rows) TF_CUDA(cudaMalloc((void**)&h->da_rows, sizeof(double) * n_da));
     {
-        std::vector<double> tmp(g.ny + 2, 0.0);
-        for (int y = 0; y < g.ny; ++y) tmp[y + 1] = da_rows[y];
-        tmp[0] = da_rows[0]; tmp[g.ny + 1] = da_rows[g.ny - 1];
-        TF_CUDA(cudaMemcpy(h->da_rows, tmp.data(), sizeof(double) * (g.ny + 2), cudaMemcpyHostToDevice));
+        // apron slots start as copies of the edge rows; a strip with neighbours
+        // gets the neighbours' values in chan_exchange_static (tf_chan_layout.cu)
+        std::vector<double> tmp(n_da, 0.0);
+        for (int y = -TF_APRON; y < g.ny + TF_APRON; ++y)
+            tmp[y + TF_APRON] = da_rows[y < 0 ? 0 : (y >= g.ny ? g.ny - 1 : y)];
+        TF_CUDA(cudaMemcpy(h->da_rows, tmp.data(), sizeof(double) * n_da, cudaMemcpyHostToDevice));
     }
     // state rasters
     TF_TRY(raster_alloc(h, h->vol, 0));
@@ -62,6 +65,20 @@ extern "C" int tf_chan_init(tf_handle h, int wave, int law, double dt, const dou
     TF_TRY(raster_alloc(h, h->Qb, 0));
     TF_TRY(raster_alloc(h, h->mstate, 0));
     if (wave == TF_DYNAMIC) TF_TRY(raster_alloc(h, h->u2, 0));
+    // A handle may be initialised again (new parameters, a second run): the
+    // reference zeroes u, Q and R and restarts vol / d from d0 at every
+    // initialize() (channels_base.py:900-910), so nothing of the last run may
+    // survive in rasters that raster_alloc found already allocated.
+    {
+        const size_t n64 = sizeof(double) * (size_t)g.n_alloc;
+        Raster<double>* st[] = {&h->vol, &h->d, &h->u, &h->u2, &h->Qa, &h->Qb};
+        for (Raster<double>* r : st)
+            if (r->base) TF_CUDA(cudaMemsetAsync(r->base, 0, n64, h->stream));
+        TF_CUDA(cudaMemsetAsync(h->mstate.base, 0, (size_t)g.n_alloc, h->stream));
+    }
+    h->R_is_grid = false;
+    h->R_scalar = 0.0;
+    for (int k = 0; k < TF_R_COUNT; ++k) { h->forc_is_grid[k] = false; h->forc_scalar[k] = 0.0; }
     h->Qcur = h->Qa.p; h->Qnext = h->Qb.p;
     TF_TRY(chan_layout_init(h, allow_packed));
     // outlets
@@ -118,14 +135,14 @@ extern "C" int tf_chan_set_R(tf_handle h, const double* grid, double scalar, dou
         if (sum_out) {
             // (R*da*dt) * n_pixels for a scalar R with scalar da (:1157-1158);
             // per-row da sums the same product row by row
-            std::vector<double> da(g.ny + 2);
-            TF_CUDA(cudaMemcpy(da.data(), h->da_rows, sizeof(double) * (g.ny + 2), cudaMemcpyDeviceToHost));
+            std::vector<double> da(g.ny);
+            TF_CUDA(cudaMemcpy(da.data(), h->da_rows + TF_APRON, sizeof(double) * g.ny, cudaMemcpyDeviceToHost));
             bool uniform = true;
-            for (int y = 1; y <= g.ny; ++y) uniform = uniform && (da[y] == da[1]);
-            if (uniform) *sum_out = ((scalar * da[1]) * h->dt) * ((double)g.nx * g.ny);
+            for (int y = 0; y < g.ny; ++y) uniform = uniform && (da[y] == da[0]);
+            if (uniform) *sum_out = ((scalar * da[0]) * h->dt) * ((double)g.nx * g.ny);
             else {
                 double s = 0.0;
-                for (int y = 1; y <= g.ny; ++y) s += ((scalar * da[y]) * h->dt) * g.nx;
+                for (int y = 0; y < g.ny; ++y) s += ((scalar * da[y]) * h->dt) * g.nx;
                 *sum_out = s;
             }
         }

@@ -19,7 +19,7 @@ static inline ChanArgs chan_args(tf_handle h, int y_begin, int y_end) {
     a.steps_done = h->steps_done;
     a.Rgrid = h->R_is_grid ? h->R.p : nullptr;
     a.Rs = h->R_scalar;
-    a.da_rows = h->da_rows + 1;
+    a.da_rows = h->da_rows + TF_APRON;
     a.code = h->code.p; a.inmask = h->inmask.p; a.dw = h->dw.p;
     a.mstate = h->mstate.p;
     a.mut_width = h->mut_width; a.mut_angle = h->mut_angle;
@@ -28,7 +28,7 @@ static inline ChanArgs chan_args(tf_handle h, int y_begin, int y_end) {
     a.w32 = h->w32.p; a.S32 = h->S32.p; a.n32 = h->n32.p; a.ds32 = h->ds32.p;
     a.aidx = h->aidx.p; a.lut = h->lut;
     a.kfac = h->kfac.p;
-    a.len_rows = h->len_rows;
+    a.len_rows = h->len_rows ? h->len_rows + 8 * TF_APRON : nullptr;
     a.bad = h->bad;
     return a;
 }

@@ -182,11 +182,21 @@ k_init_mstate(const ChanArgs a) {
     ld4c(a.d + i, d);
     load_shape<PACKED>(a, i, w, t, c, ds);
     ld4(a.dw + i, dwv);
+    // A depth set in the middle of a run (tf_chan_set_state after steps were
+    // taken) re-evaluates the pending test only: a cell the rule has already
+    // rewritten stays rewritten (channels_base.py:1451-1454 is permanent) and
+    // is tested with its rewritten shape.
+    int old[CPT];
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) old[k] = 0;
+    if (a.steps_done > 0) ld4c(a.mstate + i, old);
     int nw[CPT];
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
+        const int fired = old[k] & 1;
+        apply_overbank(a, fired, dwv[k], w[k], t[k], c[k]);
         const double top = w[k] + ((2.0 * d[k]) * t[k]);
-        nw[k] = (top > dwv[k]) ? 2 : 0;
+        nw[k] = fired | ((top > dwv[k]) ? 2 : 0);
     }
     st4(a.mstate + i, nw);
 }

@@ -121,12 +121,12 @@ int chan_layout_init(tf_handle h, int allow_packed) {
         if (packed && !getenv("TF_B200_NO_LEN_ROWS")) {
             std::vector<uint8_t> code((size_t)g.n_alloc);
             TF_CUDA(cudaMemcpy(code.data(), h->code.base, (size_t)g.n_alloc, cudaMemcpyDeviceToHost));
-            std::vector<float> rows((size_t)8 * g.ny, 0.0f);
+            std::vector<float> rows((size_t)8 * (g.ny + 2 * TF_APRON), 0.0f);
             bool ok = true;
             for (int y = 0; y < g.ny && ok; ++y) {
                 const uint8_t* cr = code.data() + g.origin + (int64_t)y * g.pitch;
                 const float* wr = dw.data() + g.origin + (int64_t)y * g.pitch;
-                float* r = rows.data() + (size_t)8 * y;
+                float* r = rows.data() + (size_t)8 * (y + TF_APRON);
                 bool have[6] = {false, false, false, false, false, false};
                 for (int x = 0; x < g.nx; ++x) {
                     const int cd = cr[x];
@@ -140,11 +140,18 @@ int chan_layout_init(tf_handle h, int allow_packed) {
                 }
             }
             if (ok) {
+                // apron slots: copies of the edge rows (a strip with neighbours
+                // receives the neighbours' rows in chan_exchange_static)
+                for (int k = 0; k < TF_APRON; ++k) {
+                    memcpy(rows.data() + (size_t)8 * k, rows.data() + (size_t)8 * TF_APRON, 8 * sizeof(float));
+                    memcpy(rows.data() + (size_t)8 * (g.ny + TF_APRON + k),
+                           rows.data() + (size_t)8 * (g.ny + TF_APRON - 1), 8 * sizeof(float));
+                }
                 TF_CUDA(cudaMalloc((void**)&h->len_rows, sizeof(float) * rows.size()));
                 TF_CUDA(cudaMemcpy(h->len_rows, rows.data(), sizeof(float) * rows.size(), cudaMemcpyHostToDevice));
             }
         }
-        for (int y = -1; y <= g.ny; ++y) {
+        for (int y = -TF_APRON; y < g.ny + TF_APRON; ++y) {
             float* row = dw.data() + g.origin + (int64_t)y * g.pitch;
             for (int x = 0; x < g.pitch; ++x)
                 if (y < 0 || y >= g.ny || x >= g.nx) row[x] = 3.0e38f;

@@ -13,14 +13,18 @@
 // ---------------------------------------------------------------------------
 // Device grid geometry.
 //
-// Every device raster shares one layout: (ny + 2) rows of `pitch` elements,
-// pitch = nx rounded up to 32, preceded and followed by 32 guard elements.
-// Row -1 and row ny are apron rows (the neighbour strip's edge row, or zeros
-// at a global border), so a kernel may address (y-1 .. y+1, x-1 .. x+1) of
-// any owned cell without bounds tests: x = -1 lands in the previous row's
-// padding (or, when pitch == nx, on the previous row's last cell, which is a
-// border cell with flow code 0 and never contributes).  All row starts are
-// 32-element aligned, so 128-bit loads are always legal.
+// Every device raster shares one layout: (ny + 2 * TF_APRON) rows of `pitch`
+// elements, pitch = nx rounded up to 32, preceded and followed by TF_GUARD
+// guard elements.  Rows -1 and ny are apron rows (the neighbour strip's edge
+// row, or zeros at a global border), so a kernel may address (y-1 .. y+1,
+// x-1 .. x+1) of any owned cell without bounds tests: x = -1 lands in the
+// previous row's padding (or, when pitch == nx, on the previous row's last
+// cell, which is a border cell with flow code 0 and never contributes).  The
+// second apron rows (-2 and ny + 1) exist for the fused diffusive / dynamic
+// step, which recomputes the depth of the first apron row and therefore reads
+// the discharge one row further out.  All row starts are 32-element aligned,
+// so 128-bit loads are always legal; the guards are wide enough for a 64-cell
+// window of the marching kernels to overhang a row end.
 // ---------------------------------------------------------------------------
 struct Geom {
     int nx, ny;          // owned cells
@@ -34,7 +38,8 @@ struct Geom {
 
 static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
-#define TF_GUARD 32
+#define TF_GUARD 128
+#define TF_APRON 2      // apron rows above and below the owned rows
 #define TF_STR2(x) #x
 #define TF_STR(x) TF_STR2(x)
 
@@ -122,6 +127,8 @@ struct tf_handle_s {
     float *dx = nullptr, *dy = nullptr, *dd = nullptr;   // per-row, float32
     bool have_d8 = false, have_area = false;
     int lr_periodic = 0, tb_periodic = 0;
+    float row0_len[3] = {0.f, 0.f, 0.f};  // dx, dy, dd of GLOBAL row 0 (tf_d8_set_row0_sizes)
+    bool have_row0_len = false;
     unsigned long long* counters = nullptr;   // device scratch counters [16]
 
     // ---- routing ----------------------------------------------------------
@@ -131,12 +138,11 @@ struct tf_handle_s {
     double dt = 0.0, rho = 1000.0;
     long long steps_done = 0;             // since tf_chan_init
     bool state_dirty = true;              // mstate must be rebuilt from d
-    double* da_rows = nullptr;            // device [ny + 2] (index y + 1)
+    double* da_rows = nullptr;            // device [ny + 2 * TF_APRON] (index y + TF_APRON)
     bool chan_ready = false;
     // state
     Raster<double> vol, d, u, u2, Qa, Qb, R;
     double *Qcur = nullptr, *Qnext = nullptr;   // -> Qa.p / Qb.p
-    double *ucur = nullptr, *unext = nullptr;   // dynamic wave double buffer
     bool R_is_grid = false;
     double R_scalar = 0.0;
     Raster<double> forc[TF_R_COUNT];      // fluxes of update_R handed over as grids
@@ -150,7 +156,7 @@ struct tf_handle_s {
     Raster<float> w32, S32, n32, ds32;
     Raster<uint8_t> aidx;
     double* lut = nullptr;                // device [2*256]: tan, cos
-    float* len_rows = nullptr;            // device [8*ny]: ds {diag, E/W, N/S, -}, dw {diag, E/W, N/S, -}
+    float* len_rows = nullptr;            // device [8 * (ny + 2 * TF_APRON)] (row y at 8 * (y + TF_APRON)): ds {diag, E/W, N/S, -}, dw {diag, E/W, N/S, -}
     // outlets, diversions
     int n_outlets = 0;
     int64_t* outlet_idx = nullptr;        // device

@@ -186,8 +186,8 @@ __device__ __forceinline__ float len_by_code(int code, float diag, float ew, flo
 }
 
 __global__ void __launch_bounds__(256)
-k_finalize(D8Args a, const int16_t* __restrict__ raw, const uint8_t* __restrict__ code_in,
-           uint8_t* __restrict__ code, int32_t* __restrict__ parent,
+k_finalize(D8Args a, const int16_t* __restrict__ raw, const uint8_t* code_in,
+           uint8_t* code, int32_t* __restrict__ parent,
            float* __restrict__ ds, float* __restrict__ dw,
            const float* __restrict__ dx, const float* __restrict__ dy,
            const float* __restrict__ dd) {
@@ -436,6 +436,13 @@ extern "C" int tf_d8_set_halo_dem(tf_handle h, const float* north_row, const flo
     return 0;
 }
 
+extern "C" int tf_d8_set_row0_sizes(tf_handle h, float dx0, float dy0, float dd0) {
+    TF_CHECK(h != nullptr, "null handle");
+    h->row0_len[0] = dx0; h->row0_len[1] = dy0; h->row0_len[2] = dd0;
+    h->have_row0_len = true;
+    return 0;
+}
+
 extern "C" int tf_d8_build(tf_handle h, const float* dem, const float* dx, const float* dy,
                            const float* dd, float nodata, int link_flats, int lr_periodic,
                            int tb_periodic, int64_t* stats_out) {
@@ -463,9 +470,23 @@ extern "C" int tf_d8_build(tf_handle h, const float* dem, const float* dx, const
     }
     TF_CUDA(cudaMemsetAsync(h->counters, 0, 16 * sizeof(unsigned long long), h->stream));
     D8Args a = d8_args(h);
-    // d8_global.py:209-211: the distances of row 0 are used for every row
+    // d8_global.py:209-211: the distances of row 0 -- of the GLOBAL grid -- are
+    // used for every row.  A strip further south learns them from
+    // tf_d8_set_row0_sizes or, failing that, from rank 0 over the communicator.
+    float len0[3] = {dx[0], dy[0], dd[0]};
+    if (h->have_row0_len) memcpy(len0, h->row0_len, sizeof(len0));
+    else if (h->nccl_comm) {
+        unsigned long long bits[3] = {0, 0, 0};
+        if (h->rank == 0)
+            for (int k = 0; k < 3; ++k) { uint32_t b; memcpy(&b, &len0[k], 4); bits[k] = b; }
+        TF_CUDA(cudaMemcpyAsync(h->counters + 12, bits, sizeof(bits), cudaMemcpyHostToDevice, h->stream));
+        TF_TRY(comm_allreduce_u64(h, h->stream, h->counters + 12, 3));   // sum with zeros = broadcast
+        TF_CUDA(cudaMemcpyAsync(bits, h->counters + 12, sizeof(bits), cudaMemcpyDeviceToHost, h->stream));
+        TF_CUDA(cudaStreamSynchronize(h->stream));
+        for (int k = 0; k < 3; ++k) { const uint32_t b = (uint32_t)bits[k]; memcpy(&len0[k], &b, 4); }
+    }
     k_start_codes<<<d8_grid(h), d8_block(), 0, h->stream>>>(
-        a, h->dem.p, h->raw.p, dx[0], dy[0], dd[0], nodata, link_flats != 0, h->counters);
+        a, h->dem.p, h->raw.p, len0[0], len0[1], len0[2], nodata, link_flats != 0, h->counters);
     TF_CUDA(cudaGetLastError());
     int64_t n_reps = 0;
     if (link_flats) {

@@ -85,6 +85,11 @@ class Strip(object):
         return dict(n_flats=int(stats[0]), n_pits=int(stats[1]), n_bad=int(stats[2]),
                     n_reps=int(stats[3]))
 
+    def d8_set_row0_sizes(self, dx0, dy0, dd0):
+        """dx, dy, dd of row 0 of the global grid (d8_global.py:209-211) for a
+        strip that does not hold that row."""
+        L.check(L.lib.tf_d8_set_row0_sizes(self._h, C.c_float(dx0), C.c_float(dy0), C.c_float(dd0)))
+
     def d8_set_codes(self, codes, dx, dy, dd, lr_periodic=False, tb_periodic=False):
         codes = np.ascontiguousarray(codes, dtype=np.uint8)
         assert codes.shape == (self.ny, self.nx)
