@@ -1,10 +1,19 @@
 // tf_chan.cu -- host side of the channel-routing path: device layout, the
 // per-step launch sequence and the C ABI around it.
-#include <unordered_map>
+#include <stdlib.h>
 
 #include "tf_chan_host.cuh"
 
 int chan_layout_init(tf_handle h, int allow_packed);   // tf_chan_layout.cu
+int chan_exchange_static(tf_handle h);                  // tf_chan_layout.cu
+
+// strips + marching step: phase A of the apron row reads the neighbour's R
+static int chan_exchange_R(tf_handle h) {
+    if (!h->nccl_comm || !h->use_march || h->wave == TF_KINEMATIC) return 0;
+    void* arr[1] = {h->R.p};
+    size_t es[1] = {sizeof(double)};
+    return comm_exchange_rows(h, h->stream, arr, es, 1);
+}
 
 // ---------------------------------------------------------------------------
 extern "C" int tf_chan_set_param(tf_handle h, int which, const double* grid, double scalar,
@@ -81,6 +90,18 @@ extern "C" int tf_chan_init(tf_handle h, int wave, int law, double dt, const dou
     for (int k = 0; k < TF_R_COUNT; ++k) { h->forc_is_grid[k] = false; h->forc_scalar[k] = 0.0; }
     h->Qcur = h->Qa.p; h->Qnext = h->Qb.p;
     TF_TRY(chan_layout_init(h, allow_packed));
+    // The marching kernels need the packed layout with ds / dw derived from the
+    // code; anything else (float64-only parameters, a sinuosity grid, more than
+    // 255 bank angles) runs on the tile kernels.
+    { const char* e = getenv("TF_B200_NO_MARCH");
+      h->use_march = h->packed && h->len_rows != nullptr && !(e && e[0] == '1'); }
+    { const char* e = getenv("TF_B200_SEG_ROWS"); h->seg_rows = (e && atoi(e) > 0) ? atoi(e) : 64; }
+    if (h->use_march && wave != TF_KINEMATIC) {
+        TF_TRY(raster_alloc(h, h->volB, 0));
+        TF_CUDA(cudaMemsetAsync(h->volB.base, 0, sizeof(double) * (size_t)g.n_alloc, h->stream));
+    }
+    if (h->use_march) TF_TRY(chan_exchange_static(h));
+    h->ghost_dirty = true;
     // outlets
     TF_CHECK(n_outlets >= 0 && (n_outlets == 0 || outlet_rc), "tf_chan_init: bad outlet list");
     h->n_outlets = n_outlets;
@@ -122,6 +143,7 @@ extern "C" int tf_chan_set_state(tf_handle h, int which, const double* grid) {
             tf_set_error("tf_chan_set_state: field %d is not a stored state grid", which);
             return 1;
     }
+    h->ghost_dirty = true;
     return raster_upload(h, r, grid);
 }
 
@@ -151,6 +173,7 @@ extern "C" int tf_chan_set_R(tf_handle h, const double* grid, double scalar, dou
     TF_TRY(raster_alloc(h, h->R, 0));
     TF_TRY(raster_upload(h, h->R, grid));
     h->R_is_grid = true;
+    TF_TRY(chan_exchange_R(h));
     if (sum_out) {
         if (h->partial_cap < 6 * g.ny) {
             if (h->partial) cudaFree(h->partial);
@@ -211,6 +234,7 @@ extern "C" int tf_chan_assemble_R(tf_handle h, double* sum_out) {
     k_assemble_R<<<g.ny, 256, 0, h->stream>>>(a, fa, h->R.p, h->partial);
     TF_LAUNCHED(h, h->stream, "k_assemble_R");
     h->R_is_grid = true;
+    TF_TRY(chan_exchange_R(h));
     if (sum_out) {
         std::vector<double> part(g.ny);
         TF_CUDA(cudaMemcpyAsync(part.data(), h->partial, sizeof(double) * g.ny, cudaMemcpyDeviceToHost, h->stream));

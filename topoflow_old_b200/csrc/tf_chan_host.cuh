@@ -1,6 +1,6 @@
 // tf_chan_host.cuh -- host helpers shared by the routing translation units.
 #pragma once
-#include "tf_chan_kernels2.cuh"
+#include "tf_chan_march.cuh"
 #include "tf_common.cuh"
 
 // ---------------------------------------------------------------------------
@@ -30,6 +30,11 @@ static inline ChanArgs chan_args(tf_handle h, int y_begin, int y_end) {
     a.kfac = h->kfac.p;
     a.len_rows = h->len_rows ? h->len_rows + 8 * TF_APRON : nullptr;
     a.bad = h->bad;
+    // marching kernels: the fused waves write the volume into the partner buffer
+    a.march = h->use_march ? 1 : 0;
+    a.vol_out = (h->use_march && h->wave != TF_KINEMATIC) ? h->volB.p : h->vol.p;
+    a.n_bands = 0; a.seg_rows = h->seg_rows;
+    a.has_north = g.has_north; a.has_south = g.has_south;
     return a;
 }
 

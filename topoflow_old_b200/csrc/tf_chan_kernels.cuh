@@ -70,7 +70,22 @@ struct ChanArgs {
     const double* kfac;            // kinematic + Manning: sqrt(S_bed) / n, float64
     const float* len_rows;         // [8 * row]: ds {diag, E/W, N/S, -}, dw {diag, E/W, N/S, -}; NULL: read the rasters
     long long* bad;                // [0] depth, [1] velocity: min bad global index
+    // marching kernels (tf_chan_march.cuh)
+    double* vol_out;               // ping-pong partner of vol (== vol for the tile kernels)
+    int march;                     // mstate holds two generations (see mstate_fired)
+    int n_bands, seg_rows;         // column bands per row, rows per warp task
+    int has_north, has_south;      // a neighbour strip owns row -1 / row ny
 };
+
+// Overbank state byte.  Tile kernels: bit 0 "the rule has fired", bit 1 "it
+// fires at the next step".  The marching kernels keep two generations of that
+// pair: generation g = steps_done & 1 lives in bits 2g and 2g + 1.  A step
+// reads generation g and writes generation g ^ 1 (leaving g untouched), so a
+// warp that recomputes a row owned by a neighbouring segment always finds the
+// state that row had at the start of the step, whenever the owner writes.
+__device__ __forceinline__ int mstate_fired(const ChanArgs& a, int byte) {
+    return a.march ? ((byte >> (2 * (int)(a.steps_done & 1))) & 1) : (byte & 1);
+}
 
 // ---------------------------------------------------------------------------
 template <bool PACKED>

@@ -193,10 +193,11 @@ k_init_mstate(const ChanArgs a) {
     int nw[CPT];
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
-        const int fired = old[k] & 1;
+        const int fired = mstate_fired(a, old[k]);
         apply_overbank(a, fired, dwv[k], w[k], t[k], c[k]);
         const double top = w[k] + ((2.0 * d[k]) * t[k]);
         nw[k] = fired | ((top > dwv[k]) ? 2 : 0);
+        if (a.march) nw[k] |= nw[k] << 2;        // both generations start equal
     }
     st4(a.mstate + i, nw);
 }
@@ -213,7 +214,7 @@ k_derive(const ChanArgs a, int which, int wave, double* out) {
     const int64_t i = (int64_t)y * a.pitch + x;
     const int code = a.code[i];
     const bool noflow = (code == 0);
-    const int m = a.mstate[i] & 1;
+    const int m = mstate_fired(a, a.mstate[i]);
     double w, t, c, ds, S, n;
     if (PACKED) {
         w = a.w32[i]; ds = a.ds32[i]; S = a.S32[i]; n = a.n32[i];

@@ -174,3 +174,26 @@ int chan_layout_init(tf_handle h, int allow_packed) {
     }
     return 0;
 }
+
+// Strips: the fused marching step recomputes the volume and depth of the
+// neighbour strip's edge row in this strip's apron row, so the apron row
+// needs that row's static parameters as well (once, at initialisation).
+int chan_exchange_static(tf_handle h) {
+    if (!h->nccl_comm) return 0;
+    const Geom& g = h->g;
+    void* arr[8];
+    size_t es[8];
+    int n = 0;
+    auto add = [&](void* p, size_t e) { if (p) { arr[n] = p; es[n] = e; ++n; } };
+    add(h->w32.p, 4); add(h->S32.p, 4); add(h->n32.p, 4); add(h->aidx.p, 1);
+    add(h->kfac.p, 8); add(h->inmask.p, 1);
+    TF_TRY(comm_exchange_rows(h, h->stream, arr, es, n));
+    float* L = h->len_rows;
+    TF_TRY(comm_exchange_bytes(h, h->stream, L + 8 * TF_APRON, L + 8 * (TF_APRON - 1),
+                               L + 8 * (TF_APRON + g.ny - 1), L + 8 * (TF_APRON + g.ny), 32));
+    double* A = h->da_rows;
+    TF_TRY(comm_exchange_bytes(h, h->stream, A + TF_APRON, A + TF_APRON - 1,
+                               A + TF_APRON + g.ny - 1, A + TF_APRON + g.ny, 8));
+    TF_CUDA(cudaStreamSynchronize(h->stream));
+    return 0;
+}

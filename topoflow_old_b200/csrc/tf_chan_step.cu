@@ -36,6 +36,88 @@ static int launch_phase_b(tf_handle h, cudaStream_t s, int y0, int y1) {
     return 0;
 }
 
+// ---- marching kernels (packed layout, tf_chan_march.cuh) ----------------------
+template <int WAVE, int LAW, bool RG>
+static int launch_march_t(tf_handle h, cudaStream_t s, int y0, int y1) {
+    using C = MarchCfg<WAVE, LAW, RG>;
+    static bool attr_set[64] = {false};
+    if (h->device < 64 && !attr_set[h->device]) {
+        TF_CUDA(cudaFuncSetAttribute(k_march<WAVE, LAW, RG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)C::SMEM));
+        attr_set[h->device] = true;
+    }
+    ChanArgs a = chan_args(h, y0, y1);
+    a.n_bands = (h->g.pitch + C::STRIDE - 1) / C::STRIDE;
+    const int n_segs = (y1 - y0 + a.seg_rows - 1) / a.seg_rows;
+    const long long tasks = (long long)a.n_bands * n_segs;
+    const unsigned blocks = (unsigned)((tasks + TF_MARCH_WARPS - 1) / TF_MARCH_WARPS);
+    k_march<WAVE, LAW, RG><<<blocks, TF_MARCH_WARPS * 32, C::SMEM, s>>>(a);
+    TF_LAUNCHED(h, s, "k_march");
+    h->acc_launches++;
+    return 0;
+}
+
+template <int WAVE>
+static int launch_march_w(tf_handle h, cudaStream_t s, int y0, int y1) {
+    if (h->law == 0) return h->R_is_grid ? launch_march_t<WAVE, 0, true>(h, s, y0, y1)
+                                         : launch_march_t<WAVE, 0, false>(h, s, y0, y1);
+    return h->R_is_grid ? launch_march_t<WAVE, 1, true>(h, s, y0, y1)
+                        : launch_march_t<WAVE, 1, false>(h, s, y0, y1);
+}
+
+static int launch_march(tf_handle h, cudaStream_t s, int y0, int y1) {
+    if (y1 <= y0) return 0;
+    switch (h->wave) {
+        case TF_KINEMATIC: return launch_march_w<0>(h, s, y0, y1);
+        case TF_DIFFUSIVE: return launch_march_w<1>(h, s, y0, y1);
+        default: return launch_march_w<2>(h, s, y0, y1);
+    }
+}
+
+// one marching step: a strip with neighbours computes its edge bands first on
+// the high-priority stream, so that the rows its neighbours need travel while
+// the interior is computed.  One exchange per step for every wave: the next
+// discharge (two rows for the fused waves, whose phase A of the apron row reads
+// one row further out) and, for the dynamic wave, the new velocity.
+static int march_step(tf_handle h) {
+    const Geom& g = h->g;
+    cudaStream_t s = h->stream;
+    const bool multi = h->nccl_comm != nullptr;
+    const bool fused = h->wave != TF_KINEMATIC;
+    void* arr[2] = {h->Qnext, h->u.p};
+    size_t es[2] = {sizeof(double), sizeof(double)};
+    int dep[2] = {fused ? 2 : 1, 1};
+    const int n_arr = h->wave == TF_DYNAMIC ? 2 : 1;
+    if (!multi || g.ny < 32) {
+        TF_TRY(launch_march(h, s, 0, g.ny));
+        if (multi) TF_TRY(comm_exchange_rows(h, s, arr, es, n_arr, dep));
+    } else {
+        cudaStream_t e = h->stream_edge;
+        TF_CUDA(cudaEventRecord(h->ev_main, s));
+        TF_CUDA(cudaStreamWaitEvent(e, h->ev_main, 0));
+        TF_TRY(launch_march(h, e, 0, 8));
+        TF_TRY(launch_march(h, e, g.ny - 8, g.ny));
+        TF_TRY(comm_exchange_rows(h, e, arr, es, n_arr, dep));
+        TF_CUDA(cudaEventRecord(h->ev_edge, e));
+        TF_TRY(launch_march(h, s, 8, g.ny - 8));
+        TF_CUDA(cudaStreamWaitEvent(s, h->ev_edge, 0));
+    }
+    if (fused) { Raster<double> r = h->vol; h->vol = h->volB; h->volB = r; }
+    return 0;
+}
+
+// apron copies of what a neighbour strip owns and this strip's phase A of the
+// apron row reads: refreshed after anything but a step changed them
+static int refresh_ghosts(tf_handle h) {
+    if (!h->nccl_comm) { h->ghost_dirty = false; return 0; }
+    void* arr[4] = {h->vol.p, h->mstate.p, h->Qcur, h->u2.p};
+    size_t es[4] = {sizeof(double), 1, sizeof(double), sizeof(double)};
+    int dep[4] = {1, 1, TF_APRON, 1};
+    TF_TRY(comm_exchange_rows(h, h->stream, arr, es, h->wave == TF_DYNAMIC ? 4 : 3, dep));
+    h->ghost_dirty = false;
+    return 0;
+}
+
 static int ensure_taps(tf_handle h, int n_steps) {
     const int nc = h->pts[TF_PT_CANALS_IN].n;
     if (n_steps <= h->taps_cap && h->taps && (nc == 0 || h->canal_taps)) return 0;
@@ -84,13 +166,17 @@ static int queue_steps(tf_handle h, int n_steps, int record) {
             k_diversions<<<1, 32, 0, s>>>(p, h->Qcur, h->vol.p, h->dt);
             TF_LAUNCHED(h, s, "k_diversions");
             h->acc_launches++;
-            if (multi) {   // a diverted cell on an edge row changes the neighbour's halo
+            if (multi && h->use_march) h->ghost_dirty = true;
+            else if (multi) {   // a diverted cell on an edge row changes the neighbour's halo
                 void* arr[1] = {h->Qcur};
                 size_t es[1] = {sizeof(double)};
                 TF_TRY(comm_exchange_rows(h, s, arr, es, 1));
             }
         }
-        if (h->wave == TF_KINEMATIC) {
+        if (h->use_march) {
+            if (h->ghost_dirty) TF_TRY(refresh_ghosts(h));
+            TF_TRY(march_step(h));
+        } else if (h->wave == TF_KINEMATIC) {
             if (!multi || g.ny < 32) {
                 TF_TRY(launch_kinematic(h, s, 0, g.ny));
                 if (multi) {
@@ -248,6 +334,10 @@ static double layout_bytes_per_cell(tf_handle h) {
     if (h->wave == TF_KINEMATIC) {
         b = 8 /*Q*/ + 8 /*vol r*/ + 1 + 1 + 1 /*code, mask, mstate*/ + shape + dw
             + (h->kfac.p ? 8 : sr) + R + 32 /*vol, d, u, Qnext w*/;
+    } else if (h->use_march) {
+        // one fused pass: Q, vol, code, mask, mstate, w, angle index, S, n [, u_old] in;
+        // vol, d, u, Qnext out
+        b = 8 + 8 + 3 + shape + sr + R + 32 + (h->wave == TF_DYNAMIC ? 8 : 0);
     } else {
         const double A = 8 + 8 + 3 + shape + dw + R + 16;             // phase A
         double B = 8 /*d*/ + 2 + shape + dw + sr + 16;                // phase B: u, Qn
@@ -277,7 +367,7 @@ extern "C" int tf_chan_timing(tf_handle h, double* out4) {
 }
 
 int chan_free(tf_handle h) {
-    raster_free(h->vol); raster_free(h->d); raster_free(h->u); raster_free(h->u2);
+    raster_free(h->vol); raster_free(h->volB); raster_free(h->d); raster_free(h->u); raster_free(h->u2);
     raster_free(h->Qa); raster_free(h->Qb); raster_free(h->R);
     for (int k = 0; k < TF_R_COUNT; ++k) { raster_free(h->forc[k]); h->forc_is_grid[k] = false; }
     raster_free(h->mstate);

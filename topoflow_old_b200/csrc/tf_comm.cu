@@ -97,8 +97,10 @@ extern "C" int tf_comm_init(tf_handle h, int rank, int nranks, const uint8_t* id
 // For each raster: my first row -> north neighbour's south apron, my last row
 // -> south neighbour's north apron, and the mirror receives.  One NCCL group,
 // queued on stream s.
+// depths[k] (default 1, at most TF_APRON) = how many edge rows of raster k go
+// each way: the fused marching step reads the discharge two rows out.
 int comm_exchange_rows(tf_handle h, cudaStream_t s, void* const* arrays,
-                       const size_t* elem_sizes, int n_arrays) {
+                       const size_t* elem_sizes, int n_arrays, const int* depths) {
     if (!h->nccl_comm) return 0;
     const Geom& g = h->g;
     ncclComm_t comm = (ncclComm_t)h->nccl_comm;
@@ -106,14 +108,35 @@ int comm_exchange_rows(tf_handle h, cudaStream_t s, void* const* arrays,
     for (int k = 0; k < n_arrays; ++k) {
         char* p = (char*)arrays[k];
         const size_t row = (size_t)g.pitch * elem_sizes[k];
+        const int d = depths ? depths[k] : 1;
+        TF_CHECK(d >= 1 && d <= TF_APRON && d <= g.ny, "comm_exchange_rows: depth %d", d);
         if (g.has_north) {
-            TF_NCCL(g_nccl.Send(p, row, ncclInt8, h->rank - 1, comm, s));
-            TF_NCCL(g_nccl.Recv(p - row, row, ncclInt8, h->rank - 1, comm, s));
+            TF_NCCL(g_nccl.Send(p, d * row, ncclInt8, h->rank - 1, comm, s));
+            TF_NCCL(g_nccl.Recv(p - d * row, d * row, ncclInt8, h->rank - 1, comm, s));
         }
         if (g.has_south) {
-            TF_NCCL(g_nccl.Send(p + (size_t)(g.ny - 1) * row, row, ncclInt8, h->rank + 1, comm, s));
-            TF_NCCL(g_nccl.Recv(p + (size_t)g.ny * row, row, ncclInt8, h->rank + 1, comm, s));
+            TF_NCCL(g_nccl.Send(p + (size_t)(g.ny - d) * row, d * row, ncclInt8, h->rank + 1, comm, s));
+            TF_NCCL(g_nccl.Recv(p + (size_t)g.ny * row, d * row, ncclInt8, h->rank + 1, comm, s));
         }
+    }
+    TF_NCCL(g_nccl.GroupEnd());
+    return 0;
+}
+
+// A few bytes each way between neighbouring strips (per-row tables).
+int comm_exchange_bytes(tf_handle h, cudaStream_t s, const void* send_north, void* recv_north,
+                        const void* send_south, void* recv_south, size_t bytes) {
+    if (!h->nccl_comm) return 0;
+    const Geom& g = h->g;
+    ncclComm_t comm = (ncclComm_t)h->nccl_comm;
+    TF_NCCL(g_nccl.GroupStart());
+    if (g.has_north) {
+        TF_NCCL(g_nccl.Send(send_north, bytes, ncclInt8, h->rank - 1, comm, s));
+        TF_NCCL(g_nccl.Recv(recv_north, bytes, ncclInt8, h->rank - 1, comm, s));
+    }
+    if (g.has_south) {
+        TF_NCCL(g_nccl.Send(send_south, bytes, ncclInt8, h->rank + 1, comm, s));
+        TF_NCCL(g_nccl.Recv(recv_south, bytes, ncclInt8, h->rank + 1, comm, s));
     }
     TF_NCCL(g_nccl.GroupEnd());
     return 0;

@@ -141,7 +141,10 @@ struct tf_handle_s {
     double* da_rows = nullptr;            // device [ny + 2 * TF_APRON] (index y + TF_APRON)
     bool chan_ready = false;
     // state
-    Raster<double> vol, d, u, u2, Qa, Qb, R;
+    Raster<double> vol, volB, d, u, u2, Qa, Qb, R;   // volB: ping-pong partner (fused marching step)
+    bool use_march = false;               // marching kernels (tf_chan_march.cuh) instead of the tile kernels
+    int seg_rows = 64;                    // rows per warp task of the marching kernels (TF_B200_SEG_ROWS)
+    bool ghost_dirty = true;              // apron copies of vol / mstate / Q / u must be refreshed from the neighbours
     double *Qcur = nullptr, *Qnext = nullptr;   // -> Qa.p / Qb.p
     bool R_is_grid = false;
     double R_scalar = 0.0;
@@ -203,7 +206,9 @@ int comm_free(tf_handle h);
 int output_free(tf_handle h);
 int chan_derive_to_scratch(tf_handle h, int which, const double** src_out);
 int comm_exchange_rows(tf_handle h, cudaStream_t s, void* const* arrays,
-                       const size_t* elem_sizes, int n_arrays);
+                       const size_t* elem_sizes, int n_arrays, const int* depths = nullptr);
+int comm_exchange_bytes(tf_handle h, cudaStream_t s, const void* send_north, void* recv_north,
+                        const void* send_south, void* recv_south, size_t bytes);
 int comm_allreduce_u64(tf_handle h, cudaStream_t s, unsigned long long* dev, int n);
 int comm_allgather_rows(tf_handle h, cudaStream_t s, const void* own, void* full, size_t row_bytes,
                         const int* first_row, const int* n_rows);
