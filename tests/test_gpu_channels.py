@@ -20,13 +20,13 @@ RTOL = 1e-10
 WAVES = {'kinematic': 0, 'diffusive': 1, 'dynamic': 2}
 
 
-def field_err(got, want):
+def field_err(got, want, floor=1e-9):
     got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
     assert np.array_equal(np.isnan(got), np.isnan(want)), 'NaN pattern differs'
     scale = np.nanmax(np.abs(want)) if want.size else 0.0
     if not np.isfinite(scale) or scale == 0.0:
         return float(np.nanmax(np.abs(got - want))) if want.size else 0.0
-    den = np.maximum(np.abs(want), 1e-9 * scale)
+    den = np.maximum(np.abs(want), floor * scale)
     return float(np.nanmax(np.abs(got - want) / den))
 
 
@@ -44,11 +44,11 @@ def gpu_for(c, wave, dt, allow_packed=True):
     return s
 
 
-def compare(s, ch, tag, tol=RTOL):
+def compare(s, ch, tag, tol=RTOL, u_floor=1e-9):
     from topoflow_old_b200 import _lib as L
     worst = {}
     for name, fid in (('vol', L.F_VOL), ('d', L.F_D), ('u', L.F_U), ('Q', L.F_Q)):
-        worst[name] = field_err(s.get(fid), getattr(ch, name))
+        worst[name] = field_err(s.get(fid), getattr(ch, name), u_floor if name == 'u' else 1e-9)
     assert max(worst.values()) <= tol, (tag, worst)
     return worst
 

@@ -45,7 +45,18 @@ def _route(c, wave, n_steps, d0_check=True):
         for _ in range(n_steps - 1):
             ch.update()
         assert bad[0] == -1 and bad[1] == -1
-        worst = compare(s, ch, '%s %dx%d' % (wave, c['nx'], c['ny']))
+        # The dynamic wave forms u = M / vol with M a sum of momentum terms that
+        # nearly cancel in a few cells of four million (u ~ 1e-6 of the field's
+        # maximum, from terms 1e4 times larger: measured, scripts/debug_dyn.py).
+        # There the 6e-14 relative difference that d has picked up by then (the
+        # friction factor's cube root differs from glibc's pow in the last bits,
+        # and pow has its own error) is amplified, through (d - d_parent)/ds,
+        # to 1e-9 of that tiny velocity: 2 cells of 4.2 million exceed 1e-10 of
+        # their own value, by an absolute 2e-15 m/s.  Those cells are held to
+        # 1e-14 of the field maximum (floor 1e-4) instead; vol, d and Q keep the
+        # usual bound everywhere, and u keeps it wherever |u| > 1e-4 max|u|.
+        worst = compare(s, ch, '%s %dx%d' % (wave, c['nx'], c['ny']),
+                        u_floor=1e-4 if wave == 'dynamic' else 1e-9)
         assert field_err(taps[-1, 0], np.array([ch.Q_outlet, ch.u_outlet, ch.d_outlet, ch.f_outlet],
                                                dtype=np.float64).reshape(4)) <= RTOL
         assert ch.Q.max() > 0.0

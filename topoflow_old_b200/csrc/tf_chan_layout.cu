@@ -41,7 +41,10 @@ static int fill_raster(tf_handle h, Raster<T>& r, const HostParam& p, T pad) {
         T* row = host.data() + g.origin + (size_t)y * g.pitch;
         for (int x = 0; x < g.nx; ++x) row[x] = (T)hp_at(p, (size_t)y * g.nx + x);
     }
-    TF_CUDA(cudaMemcpy(r.base, host.data(), sizeof(T) * (size_t)g.n_alloc, cudaMemcpyHostToDevice));
+    // on the handle's stream: raster_alloc has queued a memset there, and the
+    // stream is non-blocking, so a copy on the default stream could overtake it
+    TF_CUDA(cudaMemcpyAsync(r.base, host.data(), sizeof(T) * (size_t)g.n_alloc, cudaMemcpyHostToDevice, h->stream));
+    TF_CUDA(cudaStreamSynchronize(h->stream));
     return 0;
 }
 

@@ -237,9 +237,13 @@ k_march(const __grid_constant__ ChanArgs a) {
     }
     auto issue = [&](int i) {
         const int r0 = i + D + 1, r1 = i + D, r2 = i + D - 1;
-        const bool ok0 = r0 >= -TF_APRON && r0 < ny + TF_APRON;
-        const bool ok1 = r1 >= -TF_APRON && r1 < ny + TF_APRON;
-        const bool ok2 = r2 >= -TF_APRON && r2 < ny + TF_APRON;
+        // Only rows that exist and that this task will read: a copy of a row
+        // nobody needs would share its ring slot with a later, needed row while
+        // both are still in flight, and the two may land in either order.
+        const bool ok0 = r0 >= -TF_APRON && r0 < ny + TF_APRON;                      // first: yA_first - 1
+        const bool ok1 = r1 >= yA_first && r1 < ny + TF_APRON;
+        const bool ok2 = r2 >= y0 && r2 < ny + TF_APRON;
+        const bool ok3 = r1 >= y0 - 1 && r1 >= -TF_APRON && r1 < ny + TF_APRON;
         const int b0 = march_slot<C::R0>(r0) * C::QB;
         const int b1 = march_slot<C::R1>(r1) * C::C1B;
         const int b2 = march_slot<C::R2>(r2) * C::C2B;
@@ -247,7 +251,7 @@ k_march(const __grid_constant__ ChanArgs a) {
 #pragma unroll
         for (int k = 0; k < C::K; ++k) {
             const int cls = cp[k].cls & 15;
-            const bool ok = (cp[k].cls >= 0) && ((cls == 0) ? ok0 : ((cls == 2) ? ok2 : ok1));
+            const bool ok = (cp[k].cls >= 0) && ((cls == 0) ? ok0 : ((cls == 1) ? ok1 : ((cls == 2) ? ok2 : ok3)));
             const int base = (cls == 0) ? b0 : ((cls == 1) ? b1 : ((cls == 2) ? b2 : b3));
             if (ok) {
                 const unsigned dst = wsm_u + (unsigned)(cp[k].dst + base);
@@ -314,7 +318,11 @@ k_march(const __grid_constant__ ChanArgs a) {
             const uchar2 aidx2 = *reinterpret_cast<const uchar2*>(c1 + C::O_AIDX + bi);
             const float4 rs = *reinterpret_cast<const float4*>(c1 + C::O_LEN);
             const float4 rw = *reinterpret_cast<const float4*>(c1 + C::O_LEN + 16);
+#ifdef TF_MARCH_DA_DIRECT
+            const double da = a.da_rows[yA];
+#else
             const double da = *reinterpret_cast<const double*>(c1 + C::O_DA);
+#endif
             double R[2];
             if (RGRID) {
                 const double2 r2 = *reinterpret_cast<const double2*>(c1 + C::O_RG + lane * 16);

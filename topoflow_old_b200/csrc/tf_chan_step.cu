@@ -220,9 +220,9 @@ static int queue_steps(tf_handle h, int n_steps, int record) {
             TF_LAUNCHED(h, s, "k_taps");
             h->acc_launches++;
         }
+        h->steps_done++;         // the generation of the overbank byte follows the step count
     }
     h->acc_steps += n_steps;
-    h->steps_done += n_steps;
     return 0;
 }
 
