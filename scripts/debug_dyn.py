@@ -9,7 +9,7 @@ n = int(sys.argv[1])
 c = make_case(n, n, seed=3, d0=0.02)
 ch = oracle_for(c, 2, 0.5)
 for mode in ('march', 'tile'):
-    os.environ['TF_B200_NO_MARCH'] = '1' if mode == 'tile' else '0'
+    os.environ['TF_B200_MARCH'] = '0' if mode == 'tile' else '1'
     s = gpu_for(c, 2, 0.5)
     s.set_R(float(c['P_rain']))
     s.step(10)

@@ -14,7 +14,7 @@ nx, ny = int(sys.argv[1]), int(sys.argv[2])
 d0 = float(sys.argv[3]) if len(sys.argv) > 3 else 0.02
 c = make_case(nx, ny, seed=3, d0=d0)
 for mode in ('march', 'tile'):
-    os.environ['TF_B200_NO_MARCH'] = '1' if mode == 'tile' else '0'
+    os.environ['TF_B200_MARCH'] = '0' if mode == 'tile' else '1'
     ch = oracle_for(c, 0, 2.0)
     s = gpu_for(c, 0, 2.0)
     v0 = s.get(L.F_VOL)

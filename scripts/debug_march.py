@@ -17,7 +17,7 @@ c = make_case(nx, ny, seed=9, d0=0.01)
 for wave, dt in ((0, 2.0), (1, 2.0), (2, 0.5)):
     out = {}
     for mode in ('march', 'tile'):
-        os.environ['TF_B200_NO_MARCH'] = '1' if mode == 'tile' else '0'
+        os.environ['TF_B200_MARCH'] = '0' if mode == 'tile' else '1'
         s = gpu_for(c, wave, dt)
         s.set_R(float(c['P_rain']))
         res = []

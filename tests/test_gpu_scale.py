@@ -86,8 +86,8 @@ def test_ragged_wide_grid(wave):
 
 @pytest.mark.parametrize('wave', ['kinematic', 'diffusive', 'dynamic'])
 def test_marching_and_tile_kernels_agree_bit_for_bit(wave):
-    """The packed layout runs on the marching kernels, which fuse the two
-    phases of the diffusive / dynamic step; TF_B200_NO_MARCH=1 keeps it on the
+    """TF_B200_MARCH=1 runs the packed layout on the marching kernels, which
+    fuse the two phases of the diffusive / dynamic step; the default is the
     tile kernels.  Both evaluate the same expressions in the same order, so
     every field must agree exactly, seams of bands (60 / 64 columns) and of
     segments (TF_B200_SEG_ROWS rows) included."""
@@ -96,16 +96,16 @@ def test_marching_and_tile_kernels_agree_bit_for_bit(wave):
     dt = 0.5 if wave == 'dynamic' else 2.0
     out = {}
     for mode in ('march', 'march_seg7', 'tile'):
-        os.environ.pop('TF_B200_NO_MARCH', None)
+        os.environ.pop('TF_B200_MARCH', None)
         os.environ.pop('TF_B200_SEG_ROWS', None)
-        if mode == 'tile':
-            os.environ['TF_B200_NO_MARCH'] = '1'
+        if mode != 'tile':
+            os.environ['TF_B200_MARCH'] = '1'
         if mode == 'march_seg7':
             os.environ['TF_B200_SEG_ROWS'] = '7'
         try:
             s = gpu_for(c, WAVES[wave], dt)
         finally:
-            os.environ.pop('TF_B200_NO_MARCH', None)
+            os.environ.pop('TF_B200_MARCH', None)
             os.environ.pop('TF_B200_SEG_ROWS', None)
         try:
             s.set_R(float(c['P_rain']))

@@ -90,11 +90,12 @@ extern "C" int tf_chan_init(tf_handle h, int wave, int law, double dt, const dou
     for (int k = 0; k < TF_R_COUNT; ++k) { h->forc_is_grid[k] = false; h->forc_scalar[k] = 0.0; }
     h->Qcur = h->Qa.p; h->Qnext = h->Qb.p;
     TF_TRY(chan_layout_init(h, allow_packed));
-    // The marching kernels need the packed layout with ds / dw derived from the
-    // code; anything else (float64-only parameters, a sinuosity grid, more than
-    // 255 bank angles) runs on the tile kernels.
-    { const char* e = getenv("TF_B200_NO_MARCH");
-      h->use_march = h->packed && h->len_rows != nullptr && !(e && e[0] == '1'); }
+    // The marching kernels (tf_chan_march.cuh) are opt-in, TF_B200_MARCH=1: they
+    // are bit-identical to the tile kernels and move fewer bytes for the
+    // diffusive / dynamic wave, but as measured on B200 they are slower (DESIGN.md
+    // section 3b).  They need the packed layout with ds / dw derived from the code.
+    { const char* e = getenv("TF_B200_MARCH");
+      h->use_march = h->packed && h->len_rows != nullptr && h->rcp_ok && (e && e[0] == '1'); }
     { const char* e = getenv("TF_B200_SEG_ROWS"); h->seg_rows = (e && atoi(e) > 0) ? atoi(e) : 64; }
     if (h->use_march && wave != TF_KINEMATIC) {
         TF_TRY(raster_alloc(h, h->volB, 0));

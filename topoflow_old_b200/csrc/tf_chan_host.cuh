@@ -28,13 +28,14 @@ static inline ChanArgs chan_args(tf_handle h, int y_begin, int y_end) {
     a.w32 = h->w32.p; a.S32 = h->S32.p; a.n32 = h->n32.p; a.ds32 = h->ds32.p;
     a.aidx = h->aidx.p; a.lut = h->lut;
     a.kfac = h->kfac.p;
-    a.len_rows = h->len_rows ? h->len_rows + 8 * TF_APRON : nullptr;
+    a.len_rows = h->len_rows ? h->len_rows + TF_LEN_ROW * TF_APRON : nullptr;
     a.bad = h->bad;
     // marching kernels: the fused waves write the volume into the partner buffer
     a.march = h->use_march ? 1 : 0;
     a.vol_out = (h->use_march && h->wave != TF_KINEMATIC) ? h->volB.p : h->vol.p;
     a.n_bands = 0; a.seg_rows = h->seg_rows;
     a.has_north = g.has_north; a.has_south = g.has_south;
+    a.rcp_ok = h->rcp_ok ? 1 : 0;
     return a;
 }
 

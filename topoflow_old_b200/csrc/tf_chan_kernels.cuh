@@ -34,6 +34,9 @@
 #ifndef TF_LEAN_CHECKS
 #define TF_LEAN_CHECKS 1
 #endif
+#ifndef TF_TILE_RCP
+#define TF_TILE_RCP 1   /* depth divisions through precomputed reciprocals (exact, div_by_rcp) */
+#endif
 #ifndef TF_PREFETCH
 #define TF_PREFETCH 9   /* bit 0: kfac of this tile, bit 3: look-ahead of a.pf_rows rows */
 #endif
@@ -66,15 +69,16 @@ struct ChanArgs {
     // parameters, packed layout
     const float *w32, *S32, *n32, *ds32;
     const uint8_t* aidx;
-    const double* lut;             // [256] tan, [256] cos
+    const double* lut;             // [256] tan, [256] cos, [256] 1 / (2 tan)
     const double* kfac;            // kinematic + Manning: sqrt(S_bed) / n, float64
-    const float* len_rows;         // [8 * row]: ds {diag, E/W, N/S, -}, dw {diag, E/W, N/S, -}; NULL: read the rasters
+    const float* len_rows;         // [16 * row] (see tf_handle_s::len_rows): ds {diag, E/W, N/S, -}, dw {diag, E/W, N/S, -}; NULL: read the rasters
     long long* bad;                // [0] depth, [1] velocity: min bad global index
     // marching kernels (tf_chan_march.cuh)
     double* vol_out;               // ping-pong partner of vol (== vol for the tile kernels)
     int march;                     // mstate holds two generations (see mstate_fired)
     int n_bands, seg_rows;         // column bands per row, rows per warp task
     int has_north, has_south;      // a neighbour strip owns row -1 / row ny
+    int rcp_ok;                    // the reciprocal columns of len_rows / lut may be used
 };
 
 // Overbank state byte.  Tile kernels: bit 0 "the rule has fired", bit 1 "it
@@ -119,8 +123,8 @@ template <bool PACKED>
 __device__ __forceinline__ void load_lengths(const ChanArgs& a, int64_t i, int y, const int (&code)[CPT],
                                              double (&ds)[CPT], double (&dwv)[CPT]) {
     if (PACKED && a.len_rows) {
-        const float4 rs = __ldg(reinterpret_cast<const float4*>(a.len_rows + 8 * y));
-        const float4 rw = __ldg(reinterpret_cast<const float4*>(a.len_rows + 8 * y + 4));
+        const float4 rs = __ldg(reinterpret_cast<const float4*>(a.len_rows + 16 * y));
+        const float4 rw = __ldg(reinterpret_cast<const float4*>(a.len_rows + 16 * y + 4));
 #pragma unroll
         for (int k = 0; k < CPT; ++k) {
             const int cd = code[k];                      // 1,4,16,64 diagonal; 2,32 E/W; 8,128 N/S; 0
@@ -209,7 +213,7 @@ __device__ __forceinline__ void flag_bad(const ChanArgs& a, int which, int x, in
 // mass balance + trapezoid depth for CPT cells (update_flow_volume :1308-1375,
 // update_flow_depth :1379-1532).  Returns the effective shape in w, t, c.
 // ---------------------------------------------------------------------------
-template <bool PACKED>
+template <bool PACKED, bool RCP>
 __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int y, int64_t i,
                                                  double (&Q)[CPT], double (&v)[CPT], double (&d)[CPT],
                                                  double (&w)[CPT], double (&t)[CPT], double (&c)[CPT],
@@ -231,6 +235,13 @@ __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int 
     }
     const double da = a.da_rows[y];
     const double dt = a.dt;
+#if TF_TILE_RCP
+    // (RCP: measured faster in phase A, slower -- a spill -- in the kinematic kernel)
+    int aidx_of[CPT];
+#pragma unroll
+    for (int k = 0; k < CPT; ++k) aidx_of[k] = 0;
+    if (RCP && PACKED && a.len_rows && a.rcp_ok) ld4(a.aidx + i, aidx_of);
+#endif
 #pragma unroll
     for (int k = 0; k < CPT; ++k) {
         m[k] = (ms[k] & 1) | ((ms[k] >> 1) & 1);
@@ -263,7 +274,20 @@ __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int 
         acc -= Q[k] * dt;                                      // :1366
         acc = np_max0(acc);                                    // :1375
         v[k] = acc;
+#if TF_TILE_RCP
+        double dd;
+        if (RCP && PACKED && a.len_rows && a.rcp_ok) {
+            // same bits as chan_depth (div_by_rcp is exact): the reciprocals come
+            // from the row table and the angle table instead of two divisions
+            const double* rr = reinterpret_cast<const double*>(a.len_rows + 16 * y + 8);
+            const int cd = code[k];
+            const double rcp_ds = __ldg(rr + ((cd & 0x55) ? 0 : ((cd & 0x88) ? 2 : 1)));
+            const double rcp_den = m[k] && a.mut_angle ? 0.0 : __ldg(a.lut + 512 + aidx_of[k]);
+            dd = chan_depth_rcp(acc, w[k], t[k], ds[k], rcp_ds, rcp_den);
+        } else dd = chan_depth(acc, w[k], t[k], ds[k]);
+#else
         double dd = chan_depth(acc, w[k], t[k], ds[k]);
+#endif
         if (code[k] == 0) dd = 0.0;                            // :1511
         d[k] = np_max0(dd);                                    // :1526
     }
@@ -322,7 +346,7 @@ k_step_kinematic(const ChanArgs a) {
         else prefetch_slope_rough<PACKED>(a, j);
     }
 #endif
-    volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
+    volume_and_depth<PACKED, false>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
     if (KF) ld4(a.kfac + i, S);
     else load_slope_rough<PACKED>(a, i, S, n);
     bool bad_d = false, bad_u = false;
@@ -382,7 +406,7 @@ k_phase_a(const ChanArgs a) {
     if (a.pf_rows > 0 && y + a.pf_rows < a.y_end)
         prefetch_ahead_a<PACKED>(a, i + (int64_t)a.pf_rows * a.pitch);
 #endif
-    volume_and_depth<PACKED>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
+    volume_and_depth<PACKED, true>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
     st4(a.vol + i, v);
     st4(a.d + i, d);
     store_mstate(a, i, ms, m, d, w, t, dwv);

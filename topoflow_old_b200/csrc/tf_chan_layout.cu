@@ -60,9 +60,10 @@ int chan_layout_init(tf_handle h, int allow_packed) {
     TF_CHECK(T.grid.empty() == C.grid.empty(),
              "tf_chan_init: tan and cos of the bank angle must both be grids or both scalars");
 
+    h->rcp_ok = true;
     bool packed = allow_packed && f32_exact(W) && f32_exact(S) && f32_exact(N) && f32_exact(D);
     std::vector<uint8_t> aidx;
-    std::vector<double> lut(512, 0.0);
+    std::vector<double> lut(768, 0.0);   // tan, cos, 1 / (2 tan)
     if (packed) {
         // entry 0 is the rectangle (tan 0, cos 1) the overbank rule switches to
         std::map<std::pair<uint64_t, uint64_t>, int> seen;
@@ -104,8 +105,19 @@ int chan_layout_init(tf_handle h, int allow_packed) {
         HostParam A;
         A.grid.assign(aidx.begin(), aidx.end());
         TF_TRY(fill_raster<uint8_t>(h, h->aidx, A, (uint8_t)0));
-        if (!h->lut) TF_CUDA(cudaMalloc((void**)&h->lut, sizeof(double) * 512));
-        TF_CUDA(cudaMemcpy(h->lut, lut.data(), sizeof(double) * 512, cudaMemcpyHostToDevice));
+        // third column: RN(1 / (2 tan)), the reciprocal chan_depth_rcp divides by;
+        // a denominator whose reciprocal could overflow or underflow keeps the
+        // run on the tile kernels (ordinary division)
+        h->rcp_ok = true;
+        for (int k = 0; k < 256; ++k) {
+            const double den = 2.0 * lut[k];
+            if (den == 0.0) { lut[512 + k] = 0.0; continue; }
+            if (!(fabs(den) > 1e-100 && fabs(den) < 1e100)) h->rcp_ok = false;
+            lut[512 + k] = 1.0 / den;
+        }
+        if (h->lut) cudaFree(h->lut);
+        TF_CUDA(cudaMalloc((void**)&h->lut, sizeof(double) * 768));
+        TF_CUDA(cudaMemcpy(h->lut, lut.data(), sizeof(double) * 768, cudaMemcpyHostToDevice));
     } else {
         TF_TRY(fill_raster<double>(h, h->w64, W, 1.0));
         TF_TRY(fill_raster<double>(h, h->S64, S, 1.0));
@@ -124,12 +136,12 @@ int chan_layout_init(tf_handle h, int allow_packed) {
         if (packed && !getenv("TF_B200_NO_LEN_ROWS")) {
             std::vector<uint8_t> code((size_t)g.n_alloc);
             TF_CUDA(cudaMemcpy(code.data(), h->code.base, (size_t)g.n_alloc, cudaMemcpyDeviceToHost));
-            std::vector<float> rows((size_t)8 * (g.ny + 2 * TF_APRON), 0.0f);
+            std::vector<float> rows((size_t)TF_LEN_ROW * (g.ny + 2 * TF_APRON), 0.0f);
             bool ok = true;
             for (int y = 0; y < g.ny && ok; ++y) {
                 const uint8_t* cr = code.data() + g.origin + (int64_t)y * g.pitch;
                 const float* wr = dw.data() + g.origin + (int64_t)y * g.pitch;
-                float* r = rows.data() + (size_t)8 * (y + TF_APRON);
+                float* r = rows.data() + (size_t)TF_LEN_ROW * (y + TF_APRON);
                 bool have[6] = {false, false, false, false, false, false};
                 for (int x = 0; x < g.nx; ++x) {
                     const int cd = cr[x];
@@ -143,12 +155,25 @@ int chan_layout_init(tf_handle h, int allow_packed) {
                 }
             }
             if (ok) {
+                // floats 8..15 of a row: RN(1 / ds) of the three classes as float64
+                for (int y = 0; y < g.ny; ++y) {
+                    float* r = rows.data() + (size_t)TF_LEN_ROW * (y + TF_APRON);
+                    double rcp[4] = {0.0, 0.0, 0.0, 0.0};
+                    for (int k = 0; k < 3; ++k) {
+                        const double v = (double)r[k];
+                        if (v == 0.0) continue;                  // class absent in this row
+                        if (!(v > 1e-30 && v < 1e30)) h->rcp_ok = false;
+                        rcp[k] = 1.0 / v;
+                    }
+                    memcpy(r + 8, rcp, sizeof(rcp));
+                }
                 // apron slots: copies of the edge rows (a strip with neighbours
                 // receives the neighbours' rows in chan_exchange_static)
+                const size_t rb = TF_LEN_ROW * sizeof(float);
                 for (int k = 0; k < TF_APRON; ++k) {
-                    memcpy(rows.data() + (size_t)8 * k, rows.data() + (size_t)8 * TF_APRON, 8 * sizeof(float));
-                    memcpy(rows.data() + (size_t)8 * (g.ny + TF_APRON + k),
-                           rows.data() + (size_t)8 * (g.ny + TF_APRON - 1), 8 * sizeof(float));
+                    memcpy(rows.data() + (size_t)TF_LEN_ROW * k, rows.data() + (size_t)TF_LEN_ROW * TF_APRON, rb);
+                    memcpy(rows.data() + (size_t)TF_LEN_ROW * (g.ny + TF_APRON + k),
+                           rows.data() + (size_t)TF_LEN_ROW * (g.ny + TF_APRON - 1), rb);
                 }
                 TF_CUDA(cudaMalloc((void**)&h->len_rows, sizeof(float) * rows.size()));
                 TF_CUDA(cudaMemcpy(h->len_rows, rows.data(), sizeof(float) * rows.size(), cudaMemcpyHostToDevice));
@@ -192,8 +217,9 @@ int chan_exchange_static(tf_handle h) {
     add(h->kfac.p, 8); add(h->inmask.p, 1);
     TF_TRY(comm_exchange_rows(h, h->stream, arr, es, n));
     float* L = h->len_rows;
-    TF_TRY(comm_exchange_bytes(h, h->stream, L + 8 * TF_APRON, L + 8 * (TF_APRON - 1),
-                               L + 8 * (TF_APRON + g.ny - 1), L + 8 * (TF_APRON + g.ny), 32));
+    TF_TRY(comm_exchange_bytes(h, h->stream, L + TF_LEN_ROW * TF_APRON, L + TF_LEN_ROW * (TF_APRON - 1),
+                               L + TF_LEN_ROW * (TF_APRON + g.ny - 1), L + TF_LEN_ROW * (TF_APRON + g.ny),
+                               TF_LEN_ROW * sizeof(float)));
     double* A = h->da_rows;
     TF_TRY(comm_exchange_bytes(h, h->stream, A + TF_APRON, A + TF_APRON - 1,
                                A + TF_APRON + g.ny - 1, A + TF_APRON + g.ny, 8));

@@ -49,9 +49,9 @@ static int launch_march_t(tf_handle h, cudaStream_t s, int y0, int y1) {
     ChanArgs a = chan_args(h, y0, y1);
     a.n_bands = (h->g.pitch + C::STRIDE - 1) / C::STRIDE;
     const int n_segs = (y1 - y0 + a.seg_rows - 1) / a.seg_rows;
-    const long long tasks = (long long)a.n_bands * n_segs;
-    const unsigned blocks = (unsigned)((tasks + TF_MARCH_WARPS - 1) / TF_MARCH_WARPS);
-    k_march<WAVE, LAW, RG><<<blocks, TF_MARCH_WARPS * 32, C::SMEM, s>>>(a);
+    const long long tasks = (long long)a.n_bands * n_segs;          // one warp (= one block) each
+    TF_CHECK(tasks < (1ll << 31), "tf_chan_step: %lld marching tasks; raise TF_B200_SEG_ROWS", tasks);
+    k_march<WAVE, LAW, RG><<<(unsigned)tasks, 32, C::SMEM, s>>>(a);
     TF_LAUNCHED(h, s, "k_march");
     h->acc_launches++;
     return 0;

@@ -40,6 +40,7 @@ static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
 #define TF_GUARD 128
 #define TF_APRON 2      // apron rows above and below the owned rows
+#define TF_LEN_ROW 16   // floats per row of the length table (tf_handle_s::len_rows)
 #define TF_STR2(x) #x
 #define TF_STR(x) TF_STR2(x)
 
@@ -158,8 +159,10 @@ struct tf_handle_s {
     // parameters, packed layout (float32 + angle table)
     Raster<float> w32, S32, n32, ds32;
     Raster<uint8_t> aidx;
-    double* lut = nullptr;                // device [2*256]: tan, cos
-    float* len_rows = nullptr;            // device [8 * (ny + 2 * TF_APRON)] (row y at 8 * (y + TF_APRON)): ds {diag, E/W, N/S, -}, dw {diag, E/W, N/S, -}
+    double* lut = nullptr;                // device [3*256]: tan, cos, 1 / (2 tan)
+    bool rcp_ok = true;                   // every reciprocal the marching kernels divide by is safe
+    float* len_rows = nullptr;            // device [TF_LEN_ROW * (ny + 2 * TF_APRON)], row y at TF_LEN_ROW * (y + TF_APRON):
+                                          // ds {diag, E/W, N/S, -}, dw {diag, E/W, N/S, -} float32, then 1/ds {diag, E/W, N/S, -} float64
     // outlets, diversions
     int n_outlets = 0;
     int64_t* outlet_idx = nullptr;        // device
