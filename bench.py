@@ -28,7 +28,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-ALGO_BYTES = {'kinematic': 97.0, 'diffusive': 113.0, 'dynamic': 129.0}
+ALGO_BYTES = {'kinematic': 97.0, 'diffusive': 113.0, 'dynamic': 129.0}   # SURVEY.md 8(d), R a grid
+ALGO_BYTES_SCALAR_R = 8.0          # ... minus the R read when R is a 0-d scalar (89 / 105 / 121)
 WAVE_ID = {'kinematic': 0, 'diffusive': 1, 'dynamic': 2}
 DT = {'kinematic': 2.0, 'diffusive': 2.0, 'dynamic': 0.5}
 CELL = 30.0
@@ -70,18 +71,33 @@ def synth_inputs(nx, global_ny, row0, nrows, seed=20170226, n_procs=1):
     return dem, north, south, nval, width, angle
 
 
-def build_strip(args, rank, nranks, device, unique_id=None, reduce_min=None):
+def workload_text(args, nranks):
+    return 'synthetic %dx%d fractal DEM %s, %s-wave channels, Manning, uniform rain pulse (0-d R), D8 built on GPU' % (
+        args.size, args.size, 'per GPU' if args.scaling == 'weak' else 'cut into %d row strips' % nranks, args.wave)
+
+
+def global_rows(args, nranks):
+    """Rows of the global grid: weak scaling gives every GPU size x size cells,
+    strong scaling cuts one size x size grid into nranks strips."""
+    return args.size * nranks if args.scaling == 'weak' else args.size
+
+
+def build_strip(args, rank, nranks, device, unique_id=None, reduce_min=None, nx=None, global_ny=None,
+                wave=None, want_area=False, quiet=False):
     """D8 grid and routing state of this rank's strip, ready to step."""
     from topoflow_old_b200 import _lib as L
     from topoflow_old_b200.engine import Strip
     from topoflow_old_b200.routing import setup_channels
     from topoflow_old_b200.utils import synth
     from topoflow_old_b200 import strips
-    nx, global_ny = args.size, args.size * nranks          # weak scaling: size^2 cells per GPU
+    wave = wave or args.wave
+    nx = nx or args.size
+    global_ny = global_ny or global_rows(args, nranks)
     row0, ny = strips.strip_rows(global_ny, nranks, rank)
+    log_ = (lambda *a: None) if quiet else log
     t0 = time.time()
     dem, north, south, nval, width, angle = synth_inputs(nx, global_ny, row0, ny, n_procs=nranks)
-    log('[rank %d] synthetic inputs %.1fs' % (rank, time.time() - t0))
+    log_('[rank %d] synthetic inputs %.1fs' % (rank, time.time() - t0))
     s = Strip(nx, ny, device=device)
     if nranks > 1:
         s.set_strip(row0, global_ny, rank > 0, rank < nranks - 1)
@@ -90,7 +106,8 @@ def build_strip(args, rank, nranks, device, unique_id=None, reduce_min=None):
     dd = np.full(ny, np.float32(np.sqrt(np.float64(CELL) ** 2 * 2)), dtype=np.float32)
     t0 = time.time()
     stats = s.d8_build(dem, dx, dx, dd)
-    log('[rank %d] D8 build %.2fs %s' % (rank, time.time() - t0, stats))
+    log_('[rank %d] D8 build %.2fs %s' % (rank, time.time() - t0, stats))
+    s.d8_stats = stats
     code = s.d8_get(L.D8_CODE)
     ds = s.d8_get(L.D8_DS)
     dw = s.d8_get(L.D8_DW)
@@ -102,12 +119,108 @@ def build_strip(args, rank, nranks, device, unique_id=None, reduce_min=None):
     angle *= np.pi / 180.0                                   # :2191
     outlets = [(ny // 2, nx // 2), (ny - 2, nx - 2)]
     t0 = time.time()
-    setup_channels(s, WAVE_ID[args.wave], L.MANNING, DT[args.wave], CELL * CELL, np.float64(slope),
+    if want_area:
+        t1 = time.time()
+        s.d8_area(CELL * CELL, units_km=True)
+        s.area_seconds = time.time() - t1
+    s.noflow_fraction = float((code == 0).mean())
+    setup_channels(s, WAVE_ID[wave], L.MANNING, DT[wave], CELL * CELL, np.float64(slope),
                    width, angle, np.float64(nval), sinu=1.0, d0=0.0, outlets=outlets,
                    allow_packed=not args.generic, ds=ds, reduce_min=reduce_min)
-    log('[rank %d] routing setup %.1fs' % (rank, time.time() - t0))
+    log_('[rank %d] routing setup %.1fs' % (rank, time.time() - t0))
     s.set_R(RAIN_MPS)
+    s.host_inputs = dict(slope=np.float64(slope), width=width, angle=angle, nval=np.float64(nval),
+                         code=code, ds=ds) if quiet else None
     return s
+
+
+# ---------------------------------------------------------------------------
+# parity before timing: strips == one strip (bit for bit) == oracle (1e-10)
+# ---------------------------------------------------------------------------
+PARITY_NX, PARITY_ROWS_PER_RANK, PARITY_STEPS = 2048, 256, 8
+
+
+def _field_err(got, want, floor=1e-9):
+    """max |got - want| / max(|want|, floor * max|want|), as tests/test_gpu_channels.py."""
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    if not np.array_equal(np.isnan(got), np.isnan(want)):
+        return float('inf')
+    scale = np.nanmax(np.abs(want)) if want.size else 0.0
+    if not np.isfinite(scale) or scale == 0.0:
+        return float(np.nanmax(np.abs(got - want))) if want.size else 0.0
+    return float(np.nanmax(np.abs(got - want) / np.maximum(np.abs(want), floor * scale)))
+
+
+def parity_leg(args, D):
+    """A 2048 x (256 N) grid routed three ways, for all three waves: cut into the
+    N strips of this run (halo rows over NCCL), as one strip on rank 0, and by
+    the NumPy oracle on rank 0.  Strips and the single strip must agree bit for
+    bit (D8 codes, contributing area, vol, d, u, Q); the device and the oracle
+    within 1e-10 (codes and area exactly).  Returns the dict for the JSON line
+    (rank 0) -- the caller exits non-zero when `ok` is false."""
+    from topoflow_old_b200 import _lib as L
+    from topoflow_old_b200.engine import Strip
+    nx, gny = PARITY_NX, PARITY_ROWS_PER_RANK * D.world
+    fields = (('vol', L.F_VOL), ('d', L.F_D), ('u', L.F_U), ('Q', L.F_Q))
+    out = {'grid': [gny, nx], 'steps': PARITY_STEPS, 'strips': D.world, 'waves': {}}
+    strips_equal, worst, codes_ok, area_ok = True, 0.0, True, True
+    oracle_d8 = None
+    t_start = time.time()
+    for wave in ('kinematic', 'diffusive', 'dynamic'):
+        uid = None
+        if D.world > 1:
+            uid = Strip.comm_unique_id() if D.rank == 0 else np.zeros(128, dtype=np.uint8)
+            uid = D.bcast_bytes(uid)
+        s = build_strip(args, D.rank, D.world, D.local_rank, uid,
+                        reduce_min=(lambda v: -D.max(-v)) if D.world > 1 else None,
+                        nx=nx, global_ny=gny, wave=wave, want_area=True, quiet=True)
+        _, _, bad = s.step(PARITY_STEPS)
+        mine = {n: s.get(f) for n, f in fields}
+        mine['code'] = s.d8_get(L.D8_CODE)
+        mine['area'] = s.d8_get(L.D8_AREA)
+        mine['bad'] = bad.copy()
+        s.close()
+        parts = D.gather(mine)
+        if D.rank != 0:
+            continue
+        whole = {k: np.concatenate([p[k] for p in parts], axis=0) for k in mine if k != 'bad'}
+        no_bad = all(int(p['bad'][0]) == -1 and int(p['bad'][1]) == -1 for p in parts)
+        one = build_strip(args, 0, 1, D.local_rank, None, None, nx=nx, global_ny=gny, wave=wave,
+                          want_area=True, quiet=True)
+        one.step(PARITY_STEPS)
+        single = {n: one.get(f) for n, f in fields}
+        single['code'] = one.d8_get(L.D8_CODE)
+        single['area'] = one.d8_get(L.D8_AREA)
+        inp = one.host_inputs
+        one.close()
+        eq = all(np.array_equal(whole[k], single[k]) for k in single)
+        strips_equal = strips_equal and eq and no_bad
+        # ---- the oracle on the same inputs (rank 0, host) ----
+        from oracle import channels as och
+        from oracle import d8 as od8
+        if oracle_d8 is None:
+            dem = synth_inputs(nx, gny, 0, gny)[0]
+            oracle_d8 = od8.build(dem, CELL, CELL)
+            oracle_d8['A'] = od8.area_grid_fast(oracle_d8['d8_grid'], np.float64(CELL * CELL), 'km^2')
+        codes_ok = codes_ok and np.array_equal(single['code'], oracle_d8['d8_grid'])
+        area_ok = area_ok and np.array_equal(single['area'].view(np.uint32), oracle_d8['A'].view(np.uint32))
+        ch = och.ChannelsOracle(oracle_d8, WAVE_ID[wave], dt=DT[wave], da=np.float64(CELL * CELL),
+                                slope=inp['slope'].copy(), width=np.float64(inp['width']).copy(),
+                                angle=np.float64(inp['angle']).copy(), nval=inp['nval'].copy(),
+                                outlet_ID=(gny // 2, nx // 2))
+        ch.P_rain = och.scalar(RAIN_MPS)
+        for _ in range(PARITY_STEPS):
+            ch.update()
+        errs = {n: _field_err(single[n], getattr(ch, n)) for n, _ in fields}
+        worst = max(worst, max(errs.values()))
+        out['waves'][wave] = {'strips_bit_identical': bool(eq and no_bad), 'oracle_rel_err': max(errs.values())}
+    if D.rank != 0:
+        return None
+    out.update(strips_bit_identical=bool(strips_equal), oracle_rel_err=worst,
+               d8_codes_equal_oracle=bool(codes_ok), area_equal_oracle=bool(area_ok),
+               tolerance=1e-10, seconds=round(time.time() - t_start, 1))
+    out['ok'] = bool(strips_equal and codes_ok and area_ok and worst <= 1e-10)
+    return out
 
 
 # ---------------------------------------------------------------------------
@@ -245,9 +358,71 @@ class Dist(object):
         self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
         return float(t.item())
 
+    def gather(self, obj):
+        """obj of every rank, in rank order (a list on every rank)."""
+        if self.world == 1:
+            return [obj]
+        out = [None] * self.world
+        self.dist.all_gather_object(out, obj)
+        return out
+
     def close(self):
         if self.world > 1:
             self.dist.destroy_process_group()
+
+
+def time_steps(s, D, K, W):
+    """W untimed + K timed steps of a ready strip set; (max-over-ranks ms, launches)."""
+    s.step_async(W)
+    s.sync()
+    s.timing()
+    D.barrier()
+    if D.world > 1:
+        s.step_async(1)
+        s.sync()
+        s.timing()
+    s.step_async(K)
+    ms_dev, _, launches, _ = s.timing()
+    s.sync()
+    D.barrier()
+    return D.max(ms_dev), launches
+
+
+def strong_leg(args, D):
+    """BASELINE.json configs[3] next to the headline, whenever several GPUs run:
+    ONE 16384 x 16384 grid, dynamic wave, cut into N row strips (strong scaling),
+    and the same grid on rank 0 alone for the efficiency."""
+    import copy
+    a = copy.copy(args)
+    a.wave, a.scaling, a.size = 'dynamic', 'strong', args.strong_size
+    uid = Strip_uid(D)
+    s = build_strip(a, D.rank, D.world, D.local_rank, uid, reduce_min=lambda v: -D.max(-v), quiet=True)
+    ms, launches = time_steps(s, D, args.steps, max(args.warmup, 3))
+    _, _, bad = s.step(1)
+    s.close()
+    one_ms = None
+    if D.rank == 0:
+        one = build_strip(a, 0, 1, D.local_rank, None, None, quiet=True)
+        one.step_async(max(args.warmup, 3)); one.sync(); one.timing()
+        one.step_async(args.steps)
+        one_ms = one.timing()[0]
+        one.close()
+    D.barrier()
+    if D.rank != 0:
+        return None
+    cells = float(a.size) * a.size
+    return {'workload': workload_text(a, D.world), 'scaling': 'strong', 'n_gpus': D.world,
+            'ms_per_step': ms / args.steps, 'value': cells * args.steps / (ms * 1e-3), 'unit': 'cell-updates/s',
+            'single_gpu_ms_per_step': one_ms / args.steps,
+            'efficiency': (one_ms / ms) / D.world, 'bad_flags': [int(bad[0]), int(bad[1])]}
+
+
+def Strip_uid(D):
+    from topoflow_old_b200.engine import Strip
+    if D.world == 1:
+        return None
+    uid = Strip.comm_unique_id() if D.rank == 0 else np.zeros(128, dtype=np.uint8)
+    return D.bcast_bytes(uid)
 
 
 def run_gpu(args):
@@ -259,13 +434,28 @@ def run_gpu(args):
     if D.world > 1:
         uid = Strip.comm_unique_id() if D.rank == 0 else np.zeros(128, dtype=np.uint8)
         uid = D.bcast_bytes(uid)
+    # ---- parity first: a run whose strips or whose arithmetic are wrong is not timed ----
+    parity = None
+    if not args.no_parity:
+        parity = parity_leg(args, D)
+        ok = D.max(0.0 if (parity is None or parity['ok']) else 1.0) == 0.0
+        if D.rank == 0:
+            log('parity: %s' % json.dumps(parity))
+        if not ok:
+            if D.rank == 0:
+                print(json.dumps({'error': 'parity check failed', 'parity': parity}), file=_OUT, flush=True)
+            D.close()
+            sys.exit(3)
     s = build_strip(args, D.rank, D.world, D.local_rank, uid,
-                    reduce_min=(lambda v: -D.max(-v)) if D.world > 1 else None)
+                    reduce_min=(lambda v: -D.max(-v)) if D.world > 1 else None,
+                    want_area=args.with_area)
     # torch creates its own communicator lazily at the first collective: do that (and let every
     # rank finish its set-up) well before the timed region, or the skew lands inside it
     D.barrier()
     D.max(0.0)
-    cells = float(args.size) * args.size              # per GPU
+    cells = float(s.nx) * s.ny                        # per GPU
+    area_s = D.max(getattr(s, 'area_seconds', 0.0)) if args.with_area else None
+    noflow = D.sum(s.noflow_fraction) / D.world
     K, W = args.steps, max(args.warmup, 0)
 
     # ---- device-resident throughput ("value") -------------------------------
@@ -290,7 +480,8 @@ def run_gpu(args):
     wall_ms = (time.perf_counter() - t0) * 1e3
     log('[rank %d] %d steps: %.3f ms on the device (%.4f ms/step)' % (D.rank, K, ms_dev, ms_dev / K))
     ms = D.max(ms_dev)
-    value = cells * D.world * K / (ms * 1e-3)
+    total_cells = D.sum(cells)
+    value = total_cells * K / (ms * 1e-3)
 
     # ---- end to end: one public call per step, host buffers -------------------
     D.barrier()
@@ -301,7 +492,7 @@ def run_gpu(args):
         taps, _, bad = s.step(1)                      # outlet Q,u,d,f + bad-value flags back
     D.barrier()
     e2e_s = D.max(time.perf_counter() - t0)
-    e2e = cells * D.world * Ke / e2e_s
+    e2e = total_cells * Ke / e2e_s
     clocks = sampler.summary()
     assert bad[0] == -1 and bad[1] == -1, 'bad depth / velocity flagged: %s' % bad
 
@@ -309,7 +500,7 @@ def run_gpu(args):
     e2e_grid = None
     if not args.no_grid_rain:
         from topoflow_old_b200 import _lib as L
-        P = s.pinned_array((args.size, args.size), np.float64)
+        P = s.pinned_array((s.ny, s.nx), np.float64)
         P[:] = RAIN_MPS
         for k in range(1, 6):
             s.set_forcing(k, 0.0)
@@ -321,32 +512,53 @@ def run_gpu(args):
             s.assemble_R(want_sum=True)               # R and the vol_R increment, on the device
             taps, _, bad = s.step(1)
         D.barrier()
-        e2e_grid = cells * D.world * Kg / D.max(time.perf_counter() - t0)
+        e2e_grid = total_cells * Kg / D.max(time.perf_counter() - t0)
         s.set_R(RAIN_MPS, want_sum=False)
     s.timing()
+    strong = None
+    if D.world > 1 and args.scaling == 'weak' and not args.no_strong_leg:
+        s.sync()
+        strong = strong_leg(args, D)
 
     line = None
     peak, peak_src = peaks()
     if D.rank == 0:
-        kernel_ms = ms_dev / K                        # one fused kernel per step (kinematic)
-        achieved = ALGO_BYTES[args.wave] * cells / (kernel_ms * 1e-3) / 1e9
+        # the step kernels of one time step (one fused kernel for the kinematic wave, phase A +
+        # phase B for the other two), timed together with CUDA events on the launching stream
+        kernel_ms = ms_dev / K
+        algo = ALGO_BYTES[args.wave] - ALGO_BYTES_SCALAR_R        # the bench's R is a 0-d scalar
+        achieved = algo * cells / (kernel_ms * 1e-3) / 1e9
         traffic = None
         tp = os.path.join(ROOT, 'profiles', 'traffic_%s.json' % args.wave)
         if os.path.exists(tp):
             tj = json.load(open(tp))
-            if tj.get('size') == args.size:
+            if tj.get('size') == args.size and args.scaling == 'weak' and not args.generic:
                 traffic = tj.get('dram_bytes_per_launch')
+        # the bytes that really cross the HBM pins: ncu's DRAM counters when a capture of this
+        # size exists, else the layout's own count (ncu confirms they agree to 1 %)
+        actual_bytes = traffic if traffic is not None else layout_bytes * cells
+        frac_actual = actual_bytes / (kernel_ms * 1e-3) / 1e9 / peak
         line = {
             'metric': 'grid cell-updates/sec (fp64 routing step)', 'value': value,
             'unit': 'cell-updates/s', 'n_gpus': D.world, 'steps': K, 'warmup': W,
-            'ms_per_step': ms / K, 'higher_is_better': True, 'scaling': 'weak',
+            'ms_per_step': ms / K, 'higher_is_better': True, 'scaling': args.scaling,
             'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-            'config': {'workload': 'synthetic %dx%d fractal DEM per GPU, %s-wave channels, Manning, '
-                                   'uniform rain pulse, D8 built on GPU' % (args.size, args.size, args.wave),
-                       'grid_per_gpu': [args.size, args.size], 'wave': args.wave,
+            'config': {'workload': workload_text(args, D.world),
+                       'grid_per_gpu': [int(s.ny), int(s.nx)], 'wave': args.wave,
+                       'noflow_fraction': noflow,
+                       'pits': 'DEM not pit-filled (as FILL_PITS_IN_Z0 = 0 in the shipped cfgs): %d pits, each a '
+                               'no-flow sink' % int(s.d8_stats['n_pits']),
                        'layout': 'generic-f64' if args.generic else 'packed (exact f32 params + angle table)',
                        'l2_policy': 'inputs larger than L2 (%.1f GB touched per step)' % (layout_bytes * cells / 1e9),
-                       'parallelism': 'row strips x%d, 1 halo row of Q per step over NCCL' % D.world},
+                       'parallelism': 'row strips x%d, halo rows over NCCL (%s)' % (
+                           D.world, {'kinematic': 'Q once per step', 'diffusive': 'd between the phases, Q at the end',
+                                     'dynamic': 'd between the phases, Q and u at the end'}[args.wave])},
+            'parity': parity,
+            'strong_scaling_dynamic': strong,
+            'd8_area': None if area_s is None else {
+                'seconds': area_s, 'cells_per_s': total_cells / area_s if area_s else None,
+                'note': 'tf_d8_area, host call to host return; on strips every rank gathers the code grid '
+                        'and accumulates the whole grid (replicas, SURVEY 8e)'},
             'e2e': {'value': e2e, 'unit': 'cell-updates/s', 'h2d_bytes_per_step': 8 * 6,
                     'd2h_bytes_per_step': 8 * 4 * s.n_outlets + 16},
             'e2e_grid_rain': None if e2e_grid is None else {
@@ -357,9 +569,11 @@ def run_gpu(args):
             'gpu_launches': int(launches),
             'clocks': clocks,
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                         'frac': achieved / peak, 'traffic': traffic,
+                         'frac': achieved / peak, 'traffic': traffic, 'frac_actual': frac_actual,
+                         'actual_bytes_source': 'ncu dram bytes (profiles/traffic_%s.json)' % args.wave
+                                                if traffic is not None else 'layout bytes per cell x cells',
                          'peak_source': peak_src,
-                         'algorithmic_bytes_per_cell': ALGO_BYTES[args.wave],
+                         'algorithmic_bytes_per_cell': algo,
                          'layout_bytes_per_cell': layout_bytes,
                          'kernel_ms': kernel_ms},
             'wall_ms_timed_region': wall_ms,
@@ -398,11 +612,11 @@ def run_reference(args):
     line = {
         'impl': 'reference', 'metric': 'grid cell-updates/sec (fp64 routing step)', 'value': v,
         'unit': 'cell-updates/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
-        'ms_per_step': el / args.steps * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+        'ms_per_step': el / args.steps * 1e3, 'higher_is_better': True, 'scaling': args.scaling,
         'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-        'config': {'workload': 'synthetic %dx%d fractal DEM per GPU, %s-wave channels, Manning, '
-                               'uniform rain pulse, D8 built on GPU' % (args.size, args.size, args.wave),
-                   'grid_per_gpu': [args.size, args.size], 'wave': args.wave,
+        'config': {'workload': workload_text(args, args.gpus),
+                   'grid_per_gpu': [args.size if args.scaling == 'weak' else args.size // max(args.gpus, 1),
+                                    args.size], 'wave': args.wave,
                    'sample': 'each step = one update of the reference algorithm on a %dx%d sample of '
                              'that workload (same generator, same parameters), host cores only' % (size, size)},
         'cpu_baseline': {'value': v, 'unit': 'cell-updates/s', 'cores': 1, 'kind': 'port',
@@ -439,6 +653,13 @@ def main():
     ap.add_argument('--cpu-steps', type=int, default=25)
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--no-grid-rain', action='store_true', help='skip the extra e2e leg with a rain grid per step')
+    ap.add_argument('--scaling', default='weak', choices=['weak', 'strong'],
+                    help='weak: --size rows per GPU; strong: one --size x --size grid cut into N strips')
+    ap.add_argument('--with-area', action='store_true', help='also compute (and time) the D8 contributing area')
+    ap.add_argument('--no-parity', action='store_true', help='skip the strips / single strip / oracle check')
+    ap.add_argument('--no-strong-leg', action='store_true',
+                    help='N > 1: skip the extra strong-scaling line (dynamic wave, one grid cut into N strips)')
+    ap.add_argument('--strong-size', type=int, default=16384)
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)
