@@ -83,7 +83,7 @@ def global_rows(args, nranks):
 
 
 def build_strip(args, rank, nranks, device, unique_id=None, reduce_min=None, nx=None, global_ny=None,
-                wave=None, want_area=False, quiet=False):
+                wave=None, want_area=False, quiet=False, keep_dem=False):
     """D8 grid and routing state of this rank's strip, ready to step."""
     from topoflow_old_b200 import _lib as L
     from topoflow_old_b200.engine import Strip
@@ -112,6 +112,7 @@ def build_strip(args, rank, nranks, device, unique_id=None, reduce_min=None, nx=
     ds = s.d8_get(L.D8_DS)
     dw = s.d8_get(L.D8_DW)
     slope = synth.d8_slope(dem, code, ds, north=north, south=south)
+    s.dem_host = dem if keep_dem else None
     del dem
     width = np.float64(width)
     width[width == 0] = dw[width == 0]                       # channels_base.py:2182-2183
@@ -425,6 +426,96 @@ def Strip_uid(D):
     return D.bcast_bytes(uid)
 
 
+def coupled_forcing(nx, global_ny, row0, nrows, dem_lo, dem_hi, dem):
+    """Inputs of the provider chain on this strip (BASELINE.json configs[4]): rain and soil
+    conductivity vary cell by cell, the air temperature falls with elevation (+6 .. -6 deg C,
+    so the upper part of the grid holds snow), the radiation terms are uniform."""
+    from topoflow_old_b200.utils import synth
+    u = lambda seed: synth.uniform_field(nx, global_ny, 0.0, 1.0, row0=row0, nrows=nrows, seed=seed, dtype=np.float64)
+    T_air = 6.0 - 12.0 * (np.float64(dem) - dem_lo) / max(dem_hi - dem_lo, 1e-9)
+    met = dict(dt=60.0, P=(200.0 / 3.6e6) * (0.5 + u(51)), T_air=T_air, T_surf=T_air - 1.0, Qn_SW=300.0,
+               Qn_LW=-50.0, rain_duration=1800.0)
+    snow = dict(dt=60.0, c0=2.7, T0=-0.2, h0_snow=0.3 * u(52), h0_swe=0.1 * u(52), rho_snow=300.0)
+    evap = dict(dt=60.0, alpha=1.2, K_soil=0.45, soil_x=0.05, T_soil_x=0.0)
+    infil = dict(dt=60.0, Ks=7.2e-6 * (0.5 + u(53)), Ki=1e-7, qs=0.485, qi=0.375808, G=0.724)
+    return met, snow, evap, infil
+
+
+def run_coupled(args):
+    """met + degree-day snow + Priestley-Taylor evaporation + Green-Ampt infiltration + kinematic
+    routing under EMELI's loop, every provider on the device (topoflow_old_b200/coupled.py).  A step
+    is one channel step (dt 2 s); the providers update every 60 s = 30 steps, so K timed steps
+    hold K / 30 rounds of provider kernels and re-assemblies of R."""
+    from topoflow_old_b200.coupled import CoupledRun
+    D = Dist(args.gpus)
+    args.wave = 'kinematic'
+    uid = Strip_uid(D)
+    s = build_strip(args, D.rank, D.world, D.local_rank, uid,
+                    reduce_min=(lambda v: -D.max(-v)) if D.world > 1 else None, keep_dem=True)
+    dem = s.dem_host
+    lo, hi = -D.max(-float(dem.min())), D.max(float(dem.max()))
+    global_ny = global_rows(args, D.world)
+    from topoflow_old_b200 import strips
+    row0, ny = strips.strip_rows(global_ny, D.world, D.rank)
+    met, snow, evap, infil = coupled_forcing(s.nx, global_ny, row0, ny, lo, hi, dem)
+    del dem
+    s.dem_host = None
+    t0 = time.time()
+    run = CoupledRun(s, DT['kinematic'], met, snow, evap, infil)
+    del met, snow, evap, infil
+    log('[rank %d] providers on the device %.1fs' % (D.rank, time.time() - t0))
+    K, W = args.steps, max(args.warmup, 3)
+    dt = DT['kinematic']
+    sampler = ClockSampler(D.local_rank)
+    run.run_until(dt * (1 + W))                       # (the initial pass already made one step)
+    s.sync(); s.timing()
+    D.barrier()
+    sampler.start()
+    t0 = time.perf_counter()
+    run.run_until(dt * (1 + W + K))
+    ms_dev, n_steps, launches, layout_bytes = s.timing()
+    s.sync()
+    D.barrier()
+    e2e_s = D.max(time.perf_counter() - t0)
+    ms = D.max(ms_dev)
+    clocks = sampler.summary()
+    cells = float(s.nx) * s.ny
+    total_cells = D.sum(cells)
+    assert run.bad[0] == -1 and run.bad[1] == -1, run.bad
+    peak, peak_src = peaks()
+    line = None
+    if D.rank == 0:
+        algo = ALGO_BYTES['kinematic'] + 8.0          # grid R (97 B) + its rate of change R1
+        line = {
+            'metric': 'grid cell-updates/sec (fp64 routing step)', 'value': total_cells * K / (ms * 1e-3),
+            'unit': 'cell-updates/s', 'n_gpus': D.world, 'steps': K, 'warmup': W, 'ms_per_step': ms / K,
+            'higher_is_better': True, 'scaling': args.scaling, 'vs_baseline': None, 'dtype': 'f64',
+            'data': 'synthetic',
+            'config': {'workload': 'coupled: met + snow degree-day + evap Priestley-Taylor + infil Green-Ampt (every '
+                                   '60 s, on the device) + kinematic routing (2 s), synthetic %dx%d fractal DEM %s' % (
+                                       args.size, args.size,
+                                       'per GPU' if args.scaling == 'weak' else 'cut into %d row strips' % D.world),
+                       'grid_per_gpu': [int(s.ny), int(s.nx)], 'wave': 'kinematic',
+                       'provider_updates_in_timed_region': {k: int(v[2]) for k, v in run.clock.items()},
+                       'l2_policy': 'inputs larger than L2'},
+            'e2e': {'value': total_cells * K / e2e_s, 'unit': 'cell-updates/s', 'h2d_bytes_per_step': 48,
+                    'd2h_bytes_per_step': 8 * 4 * s.n_outlets + 16,
+                    'note': 'host loop of CoupledRun.run_until: provider kernels, interpolation, R re-assembly and '
+                            'the channel steps, outlet taps copied back; no grid crosses PCIe'},
+            'gpu_launches': int(launches), 'clocks': clocks,
+            'roofline': {'bound': 'hbm', 'achieved': algo * cells / (ms / K * 1e-3) / 1e9, 'peak': peak, 'unit': 'GB/s',
+                         'frac': algo * cells / (ms / K * 1e-3) / 1e9 / peak, 'traffic': None,
+                         'peak_source': peak_src, 'algorithmic_bytes_per_cell': algo,
+                         'note': 'step kernel bytes only (grid R + R1); the provider kernels of a 60 s round are '
+                                 'inside ms_per_step but not in the byte count'},
+            'volumes_m3': run.vol,
+        }
+    s.close()
+    D.close()
+    if line is not None:
+        print(json.dumps(line), file=_OUT, flush=True)
+
+
 def run_gpu(args):
     from topoflow_old_b200.engine import Strip
     D = Dist(args.gpus)
@@ -656,6 +747,8 @@ def main():
     ap.add_argument('--scaling', default='weak', choices=['weak', 'strong'],
                     help='weak: --size rows per GPU; strong: one --size x --size grid cut into N strips')
     ap.add_argument('--with-area', action='store_true', help='also compute (and time) the D8 contributing area')
+    ap.add_argument('--coupled', action='store_true',
+                    help='configs[4]: met + snow + evap + infil providers on the device + kinematic routing')
     ap.add_argument('--no-parity', action='store_true', help='skip the strips / single strip / oracle check')
     ap.add_argument('--no-strong-leg', action='store_true',
                     help='N > 1: skip the extra strong-scaling line (dynamic wave, one grid cut into N strips)')
@@ -663,6 +756,8 @@ def main():
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)
+    elif args.coupled:
+        run_coupled(args)
     else:
         run_gpu(args)
 

@@ -300,6 +300,80 @@ int tf_sum_R_noalloc(const double* R_dev, int nx, int ny, long long pitch,
                      const double* da_rows_dev, double da, double dt,
                      double* sum_out_dev, void* stream);
 
+/* ---- device-resident providers of the excess-rain fluxes --------------------
+ * The six fluxes of update_R come, in the reference, from the meteorology,
+ * snow, evaporation and infiltration components; EMELI copies their outputs
+ * into the channels component through host arrays at every channel step
+ * (framework/emeli.py:1841-1933, time_interpolation.py:574-685).  The entry
+ * points below run the same expressions on grids that stay on the device.
+ * Every operand is given as (grid id, scalar): id >= 0 names a device grid made
+ * by tf_grid_new, id < 0 means "use the scalar" -- the reference's Grid /
+ * Scalar input types.  Grids are float64 [ny][nx] like everything else. */
+
+/* A new zero-filled device grid; its id in *gid_out.  (The arrays the provider
+ * components allocate in their initialize_computed_vars, e.g.
+ * snow_base.py:300-345, infil_green_ampt.py:330-360.)  Freed with the handle. */
+int tf_grid_new(tf_handle h, int* gid_out);
+/* Fill a device grid from a host grid (host != NULL) or with a scalar. */
+int tf_grid_set(tf_handle h, int gid, const double* host, double scalar);
+/* Copy a device grid to the host (BMI get_values of a provider's variable). */
+int tf_grid_get(tf_handle h, int gid, double* host);
+/* dst = src on the device. */
+int tf_grid_copy(tf_handle h, int src_gid, int dst_gid);
+/* out = a * t + b: the value EMELI hands a user at time t
+ * (time_interpolation.py:677). */
+int tf_grid_axpb(tf_handle h, int a_gid, double a, int b_gid, double b, double t, int out_gid);
+/* After a provider's update: the (a, b) of EMELI's linear interpolation
+ * between the previous value v1 (time t1) and the new one v2 (time t2),
+ * time_interpolation.py:91-133 -- a = (v2 - v1) / (t2 - t1), b = v2 - a t2 when
+ * EVERY cell changed (min |v2 - v1| != 0, over all strips) and t2 != t1, else
+ * a = 0, b = v2.  *linear_out (optional) tells which. */
+int tf_interp_linear(tf_handle h, int v1_gid, int v2_gid, double t1, double t2,
+                     int a_gid, int b_gid, int* linear_out);
+
+/* P_rain = P * (T_air > 0), P_snow = P * (T_air <= 0)  (met_base.py:1013-1038,
+ * :1060-1085).  Either output id may be < 0. */
+int tf_prov_met_rain(tf_handle h, int P_gid, double P, int T_air_gid, double T_air,
+                     int P_rain_gid, int P_snow_gid);
+/* One update of the degree-day snow component: meltrate
+ * (snow_degree_day.py:272-312), its cap by the snow present and the
+ * water-equivalent / depth bookkeeping (snow_base.py:365-440).  h_snow, h_swe
+ * are state grids updated in place; SM is written; *vol_SM_out (optional) gets
+ * sum((SM*da)*dt) (update_SM_integral).  Call after tf_chan_init (cell areas). */
+int tf_prov_snow_degree_day(tf_handle h, int T_air_gid, double T_air, int P_snow_gid, double P_snow,
+                            int c0_gid, double c0, int T0_gid, double T0, double rho_H2O,
+                            int rho_snow_gid, double rho_snow, double dt,
+                            int h_snow_gid, int h_swe_gid, int SM_gid, double* vol_SM_out);
+/* Priestley-Taylor evaporation rate (evap_priestley_taylor.py:290-353):
+ * ET = max(alpha (0.406 + 0.011 T_air) (Qn_SW + Qn_LW - Qc) / 2.5e9, 0),
+ * Qc = K_soil (T_soil_x - T_surf) / soil_x.  *vol_ET_out: sum((ET*da)*dt). */
+int tf_prov_evap_priestley_taylor(tf_handle h, int Qn_SW_gid, double Qn_SW, int Qn_LW_gid, double Qn_LW,
+                                  int T_air_gid, double T_air, int T_surf_gid, double T_surf,
+                                  int alpha_gid, double alpha, int K_soil_gid, double K_soil,
+                                  int soil_x_gid, double soil_x, int T_soil_x_gid, double T_soil_x,
+                                  double dt, int ET_gid, double* vol_ET_out);
+/* One update of the one-layer Green-Ampt infiltration component
+ * (infil_base.py:216-264): P_total = P_rain + SM (:500-513), IN = min(G dK dq /
+ * I + Ks, P_total) (infil_green_ampt.py:516-572), IN = P_total where P_total <
+ * Ks (infil_base.py:784-823), IN = 0 where h_table >= elev when both grids are
+ * given (:592-647), I += IN dt (:700-728).  I is state, IN is written. */
+int tf_prov_infil_green_ampt(tf_handle h, int P_rain_gid, double P_rain, int SM_gid, double SM,
+                             int Ks_gid, double Ks, int Ki_gid, double Ki, int qs_gid, double qs,
+                             int qi_gid, double qi, int G_gid, double G, int h_table_gid, int elev_gid,
+                             double dt, int I_gid, int IN_gid, double* vol_IN_out);
+
+/* Flux `which` (enum tf_forcing) of update_R as value + rate * t, both device
+ * grids or scalars: the (b, a) pair of tf_interp_linear, or (value, 0).
+ * tf_chan_assemble_R_dev then forms R0 = (P_rain + SM + GW + MR) - (ET + IN)
+ * of the values (channels_base.py:1103-1147, in that order) and R1 = the same
+ * combination of the rates; the step kernels use R = R1 * t + R0 with t the
+ * channel time of each step.  Nothing crosses PCIe.  sum0_out / sum1_out
+ * (optional): sum((R0*da)*dt) and sum((R1*da)*dt), from which the caller keeps
+ * update_R_integral (:1151-1160) as sum1 * t + sum0 per step. */
+int tf_chan_set_forcing_dev(tf_handle h, int which, int value_gid, double value,
+                            int rate_gid, double rate);
+int tf_chan_assemble_R_dev(tf_handle h, double* sum0_out, double* sum1_out);
+
 /* ---- row-strip decomposition over several GPUs ---------------------------- */
 
 /* 128-byte NCCL unique id for tf_comm_init (rank 0 creates, all ranks use).

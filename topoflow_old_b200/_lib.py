@@ -62,6 +62,22 @@ SIGNATURES = {
     'tf_host_free': (C.c_int, [C.c_void_p]),
     'tf_sum_R_noalloc': (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_void_p, C.c_double,
                                    C.c_double, C.c_void_p, C.c_void_p]),
+    'tf_grid_new': (C.c_int, [handle_t, C.POINTER(C.c_int)]),
+    'tf_grid_set': (C.c_int, [handle_t, C.c_int, _dp, C.c_double]),
+    'tf_grid_get': (C.c_int, [handle_t, C.c_int, _dp]),
+    'tf_grid_copy': (C.c_int, [handle_t, C.c_int, C.c_int]),
+    'tf_grid_axpb': (C.c_int, [handle_t, C.c_int, C.c_double, C.c_int, C.c_double, C.c_double, C.c_int]),
+    'tf_interp_linear': (C.c_int, [handle_t, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.c_int,
+                                   C.POINTER(C.c_int)]),
+    'tf_prov_met_rain': (C.c_int, [handle_t, C.c_int, C.c_double, C.c_int, C.c_double, C.c_int, C.c_int]),
+    'tf_prov_snow_degree_day': (C.c_int, [handle_t] + [C.c_int, C.c_double] * 4 + [C.c_double, C.c_int, C.c_double,
+                                                                                  C.c_double, C.c_int, C.c_int,
+                                                                                  C.c_int, _dp]),
+    'tf_prov_evap_priestley_taylor': (C.c_int, [handle_t] + [C.c_int, C.c_double] * 8 + [C.c_double, C.c_int, _dp]),
+    'tf_prov_infil_green_ampt': (C.c_int, [handle_t] + [C.c_int, C.c_double] * 7 + [C.c_int, C.c_int, C.c_double,
+                                                                                   C.c_int, C.c_int, _dp]),
+    'tf_chan_set_forcing_dev': (C.c_int, [handle_t, C.c_int, C.c_int, C.c_double, C.c_int, C.c_double]),
+    'tf_chan_assemble_R_dev': (C.c_int, [handle_t, _dp, _dp]),
     'tf_comm_unique_id': (C.c_int, [_u8p]),
     'tf_comm_init': (C.c_int, [handle_t, C.c_int, C.c_int, _u8p]),
 }

@@ -157,6 +157,7 @@ extern "C" int tf_destroy(tf_handle h) {
     cudaDeviceSynchronize();
     comm_free(h);
     output_free(h);
+    forcing_free(h);
     chan_free(h);
     d8_free(h);
     if (h->counters) cudaFree(h->counters);

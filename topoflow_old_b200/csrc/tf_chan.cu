@@ -87,7 +87,11 @@ extern "C" int tf_chan_init(tf_handle h, int wave, int law, double dt, const dou
     }
     h->R_is_grid = false;
     h->R_scalar = 0.0;
-    for (int k = 0; k < TF_R_COUNT; ++k) { h->forc_is_grid[k] = false; h->forc_scalar[k] = 0.0; }
+    h->R_rate_on = false;
+    for (int k = 0; k < TF_R_COUNT; ++k) {
+        h->forc_is_grid[k] = false; h->forc_scalar[k] = 0.0;
+        h->fdev_value[k] = h->fdev_rate[k] = nullptr; h->fdev_value_s[k] = h->fdev_rate_s[k] = 0.0;
+    }
     h->Qcur = h->Qa.p; h->Qnext = h->Qb.p;
     TF_TRY(chan_layout_init(h, allow_packed));
     // The marching kernels (tf_chan_march.cuh) are opt-in, TF_B200_MARCH=1: they
@@ -154,6 +158,7 @@ extern "C" int tf_chan_set_R(tf_handle h, const double* grid, double scalar, dou
     const Geom& g = h->g;
     if (!grid) {
         h->R_is_grid = false;
+        h->R_rate_on = false;
         h->R_scalar = scalar;
         if (sum_out) {
             // (R*da*dt) * n_pixels for a scalar R with scalar da (:1157-1158);
@@ -174,6 +179,7 @@ extern "C" int tf_chan_set_R(tf_handle h, const double* grid, double scalar, dou
     TF_TRY(raster_alloc(h, h->R, 0));
     TF_TRY(raster_upload(h, h->R, grid));
     h->R_is_grid = true;
+    h->R_rate_on = false;
     TF_TRY(chan_exchange_R(h));
     if (sum_out) {
         if (h->partial_cap < 6 * g.ny) {
@@ -235,6 +241,7 @@ extern "C" int tf_chan_assemble_R(tf_handle h, double* sum_out) {
     k_assemble_R<<<g.ny, 256, 0, h->stream>>>(a, fa, h->R.p, h->partial);
     TF_LAUNCHED(h, h->stream, "k_assemble_R");
     h->R_is_grid = true;
+    h->R_rate_on = false;
     TF_TRY(chan_exchange_R(h));
     if (sum_out) {
         std::vector<double> part(g.ny);

@@ -19,6 +19,8 @@ static inline ChanArgs chan_args(tf_handle h, int y_begin, int y_end) {
     a.steps_done = h->steps_done;
     a.Rgrid = h->R_is_grid ? h->R.p : nullptr;
     a.Rs = h->R_scalar;
+    a.Rrate = (h->R_is_grid && h->R_rate_on) ? h->R1.p : nullptr;
+    a.t_now = (double)h->steps_done * h->dt;
     a.da_rows = h->da_rows + TF_APRON;
     a.code = h->code.p; a.inmask = h->inmask.p; a.dw = h->dw.p;
     a.mstate = h->mstate.p;

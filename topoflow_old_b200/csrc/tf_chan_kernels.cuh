@@ -56,6 +56,8 @@ struct ChanArgs {
     const double* u_old;           // dynamic wave: last step's velocity
     long long steps_done;          // time steps taken since tf_chan_init
     const double* Rgrid;           // NULL -> Rs
+    const double* Rrate;           // with Rgrid: R = Rrate * t_now + Rgrid (providers being interpolated)
+    double t_now;                  // channel time at the start of this step [s]
     double Rs;
     const double* da_rows;         // [y], y = -1 .. ny
     // D8
@@ -228,8 +230,15 @@ __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int 
     load_shape<PACKED>(a, i, w, t, c, ds);
     load_lengths<PACKED>(a, i, y, code, ds, dwv);
     double R[CPT];
-    if (a.Rgrid) ld4(a.Rgrid + i, R);
-    else {
+    if (a.Rgrid) {
+        ld4(a.Rgrid + i, R);
+        if (a.Rrate) {                                     // a * t + b, time_interpolation.py:677
+            double R1[CPT];
+            ld4(a.Rrate + i, R1);
+#pragma unroll
+            for (int k = 0; k < CPT; ++k) R[k] = (R1[k] * a.t_now) + R[k];
+        }
+    } else {
 #pragma unroll
         for (int k = 0; k < CPT; ++k) R[k] = a.Rs;
     }

@@ -81,6 +81,7 @@ static int launch_march(tf_handle h, cudaStream_t s, int y0, int y1) {
 // one row further out) and, for the dynamic wave, the new velocity.
 static int march_step(tf_handle h) {
     const Geom& g = h->g;
+    TF_CHECK(!h->R_rate_on, "tf_chan_step: the marching kernels do not take an interpolated R (unset TF_B200_MARCH)");
     cudaStream_t s = h->stream;
     const bool multi = h->nccl_comm != nullptr;
     const bool fused = h->wave != TF_KINEMATIC;
@@ -368,7 +369,7 @@ extern "C" int tf_chan_timing(tf_handle h, double* out4) {
 
 int chan_free(tf_handle h) {
     raster_free(h->vol); raster_free(h->volB); raster_free(h->d); raster_free(h->u); raster_free(h->u2);
-    raster_free(h->Qa); raster_free(h->Qb); raster_free(h->R);
+    raster_free(h->Qa); raster_free(h->Qb); raster_free(h->R); raster_free(h->R1);
     for (int k = 0; k < TF_R_COUNT; ++k) { raster_free(h->forc[k]); h->forc_is_grid[k] = false; }
     raster_free(h->mstate);
     raster_free(h->w64); raster_free(h->tan64); raster_free(h->cos64);

@@ -152,6 +152,13 @@ struct tf_handle_s {
     Raster<double> forc[TF_R_COUNT];      // fluxes of update_R handed over as grids
     double forc_scalar[TF_R_COUNT] = {0, 0, 0, 0, 0, 0};
     bool forc_is_grid[TF_R_COUNT] = {false, false, false, false, false, false};
+    // device-resident providers (tf_forcing.cu)
+    std::vector<Raster<double>> grids;    // tf_grid_new
+    const double* fdev_value[TF_R_COUNT] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    const double* fdev_rate[TF_R_COUNT] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    double fdev_value_s[TF_R_COUNT] = {0, 0, 0, 0, 0, 0}, fdev_rate_s[TF_R_COUNT] = {0, 0, 0, 0, 0, 0};
+    Raster<double> R1;                    // dR/dt while a provider is being interpolated: R = R1 * t + R
+    bool R_rate_on = false;
     Raster<uint8_t> mstate;               // bit0 mutated, bit1 pending
     // parameters, generic layout (float64)
     Raster<double> w64, tan64, cos64, S64, n64, ds64;
@@ -207,6 +214,7 @@ int d8_free(tf_handle h);
 int chan_free(tf_handle h);
 int comm_free(tf_handle h);
 int output_free(tf_handle h);
+int forcing_free(tf_handle h);
 int chan_derive_to_scratch(tf_handle h, int which, const double** src_out);
 int comm_exchange_rows(tf_handle h, cudaStream_t s, void* const* arrays,
                        const size_t* elem_sizes, int n_arrays, const int* depths = nullptr);
