@@ -374,6 +374,31 @@ int tf_chan_set_forcing_dev(tf_handle h, int which, int value_gid, double value,
                             int rate_gid, double rate);
 int tf_chan_assemble_R_dev(tf_handle h, double* sum0_out, double* sum1_out);
 
+/* ---- neighbours of the path on the same D8 structures ----------------------- */
+
+/* Depression filling of a float32 DEM: the result of utils/fill_pits.py
+ * fill_pits() (:331-582, Wang & Liu's priority flood from the start cells of
+ * get_start_pixels, :178-330: edge cells and cells next to nodata).  Every cell
+ * ends at max(z, lowest pass on any path to a start cell); non-finite cells
+ * become nodata, nodata cells are walls.  The serial heap is replaced by a
+ * relaxation from above that reaches the same, unique surface (bit-identical:
+ * elevations are only ever copied).  One strip only (tf_set_strip not used).
+ *   n_raised_out  optional: cells whose elevation was raised ("Raised pixels")
+ *   n_sweeps_out  optional: passes over the grid it took */
+int tf_fill_pits(tf_handle h, const float* dem, float nodata, float* filled_out,
+                 int64_t* n_raised_out, int64_t* n_sweeps_out);
+
+/* The lateral-flow part of satzone_base.update_water_table
+ * (components/satzone_base.py:930-1008): dzw = dt (Rg - Q_gw / da), then for k =
+ * 1..8 dzw[p_k] += Q_gw[w_k] dt / da -- the scatter of update_flow_volume on
+ * the ground-water discharge, as a gather over the child mask in the same
+ * order.  Q_gw, dzw_out: float64 [ny][nx]; Rg: grid or (NULL) scalar; da_rows:
+ * float64 [ny] cell area per row (a uniform da takes the reference's
+ * "factor = dt / da" branch, :976-992, a varying one the other, :993-1008).
+ * Needs the D8 grid (tf_d8_build). */
+int tf_satzone_dzw(tf_handle h, const double* Q_gw, const double* Rg_grid, double Rg_scalar,
+                   const double* da_rows, double dt, double* dzw_out);
+
 /* ---- row-strip decomposition over several GPUs ---------------------------- */
 
 /* 128-byte NCCL unique id for tf_comm_init (rank 0 creates, all ranks use).

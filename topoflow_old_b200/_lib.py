@@ -78,6 +78,8 @@ SIGNATURES = {
                                                                                    C.c_int, C.c_int, _dp]),
     'tf_chan_set_forcing_dev': (C.c_int, [handle_t, C.c_int, C.c_int, C.c_double, C.c_int, C.c_double]),
     'tf_chan_assemble_R_dev': (C.c_int, [handle_t, _dp, _dp]),
+    'tf_fill_pits': (C.c_int, [handle_t, _fp, C.c_float, _fp, _i64p, _i64p]),
+    'tf_satzone_dzw': (C.c_int, [handle_t, _dp, _dp, C.c_double, _dp, C.c_double, _dp]),
     'tf_comm_unique_id': (C.c_int, [_u8p]),
     'tf_comm_init': (C.c_int, [handle_t, C.c_int, C.c_int, _u8p]),
 }

@@ -115,6 +115,33 @@ class Strip(object):
         L.check(L.lib.tf_d8_get(self._h, int(which), out.ctypes.data_as(C.c_void_p)))
         return out
 
+    def fill_pits(self, dem, nodata=-9999.0):
+        """utils/fill_pits.py fill_pits() on the device: (filled DEM float32,
+        number of raised cells, passes over the grid)."""
+        dem = np.ascontiguousarray(dem, dtype=np.float32)
+        assert dem.shape == (self.ny, self.nx), dem.shape
+        out = np.empty_like(dem)
+        n_raised, n_sweeps = C.c_int64(0), C.c_int64(0)
+        L.check(L.lib.tf_fill_pits(self._h, L.ptr(dem, C.c_float), C.c_float(nodata), L.ptr(out, C.c_float),
+                                   C.byref(n_raised), C.byref(n_sweeps)))
+        return out, int(n_raised.value), int(n_sweeps.value)
+
+    def satzone_dzw(self, Q_gw, Rg, da, dt):
+        """Water-table change from recharge and lateral D8 flow
+        (satzone_base.py:930-1008)."""
+        Q = _f64(Q_gw)
+        assert Q.shape == (self.ny, self.nx)
+        da_rows = np.ascontiguousarray(np.broadcast_to(np.float64(da), (self.ny,)), dtype=np.float64)
+        out = np.empty_like(Q)
+        if np.ndim(Rg) == 0:
+            L.check(L.lib.tf_satzone_dzw(self._h, L.ptr(Q, C.c_double), None, float(Rg), L.ptr(da_rows, C.c_double),
+                                         float(dt), L.ptr(out, C.c_double)))
+        else:
+            R = _f64(Rg)
+            L.check(L.lib.tf_satzone_dzw(self._h, L.ptr(Q, C.c_double), L.ptr(R, C.c_double), 0.0,
+                                         L.ptr(da_rows, C.c_double), float(dt), L.ptr(out, C.c_double)))
+        return out
+
     # -- channels -------------------------------------------------------------
     def set_param(self, which, value, is_grid=None):
         """value: 0-d / Python scalar or [ny, nx] array."""
