@@ -193,3 +193,40 @@ def test_d8_component_standalone_area(golden_dir, tmp_path):
     assert np.array_equal(c.A.view(np.uint32), want.astype(np.float32).view(np.uint32))
     assert c.resolve.sum() == 10161
     c.finalize()
+
+
+def test_update_until_and_unchanged_forcing_take_the_fast_path(golden_dir, tmp_path):
+    """update_until() queues the steps between two output times as one device
+    call, and a rain grid that has not changed is not uploaded again: same
+    files, same scalars as 600 single update() calls."""
+    from topoflow_old_b200.components import channels_kinematic_wave
+    runs = {}
+    for mode in ('stepwise', 'batched'):
+        d = stage(golden_dir, 'plane_canal', tmp_path / mode)
+        rain = np.fromfile(os.path.join(d, 'Rain_100mmph_on_right.rtg'), dtype='<f4').reshape(20, 20)
+        P = np.float64(rain * np.float32(np.float64(1) / np.float64(3600000)))
+        comp = channels_kinematic_wave.channels_component()
+        comp.initialize(cfg_file=os.path.join(d, 'Case1_channels_kinematic_wave.cfg'), SILENT=True)
+        connect_disabled_providers(comp, P)
+        uploads = []
+        real = comp.d8.strip.set_forcing
+        comp.d8.strip.set_forcing = lambda k, v: (uploads.append(k), real(k, v))[1]
+        if mode == 'stepwise':
+            for _ in range(600):
+                comp.update(-1.0)
+        else:
+            comp.update_until(3600.0)
+        assert comp.get_status() == 'updated' and float(comp.get_current_time()) == 3600.0
+        assert comp.time_index == 600
+        # the six fluxes went to the device once, not 600 times
+        assert sorted(uploads) == [0, 1, 2, 3, 4, 5]
+        runs[mode] = dict(Q=comp.get_values('channel_water_x-section__volume_flow_rate').copy(),
+                          scal=[float(getattr(comp, n)) for n in ('Q_outlet', 'Q_peak', 'T_peak', 'u_peak', 'd_peak',
+                                                                 'vol_Q', 'vol_R')], d=d)
+        comp.finalize()
+    a, b = runs['stepwise'], runs['batched']
+    assert np.array_equal(a['Q'], b['Q'])
+    assert a['scal'][:6] == b['scal'][:6]
+    assert abs(a['scal'][6] - b['scal'][6]) <= 1e-12 * abs(a['scal'][6])
+    for f in ('Case1_0D-Q.txt', 'Case1_0D-d.txt', 'Case1_0D-u.txt', 'Case1_2D-Q.rts'):
+        assert open(os.path.join(a['d'], f), 'rb').read() == open(os.path.join(b['d'], f), 'rb').read(), f
