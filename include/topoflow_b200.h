@@ -172,6 +172,19 @@ int tf_d8_get(tf_handle h, int which, void* host_out);
 int tf_chan_set_param(tf_handle h, int which, const double* grid,
                       double scalar, int is_grid_in_reference);
 
+/* The bank angle [rad] as the reference holds it (channels_base.py:2191, "angle
+ * *= deg_to_rad"), instead of TF_P_TAN_ANGLE / TF_P_COS_ANGLE grids: the library
+ * finds the distinct values on the device and returns them in ascending order
+ * (distinct_out: room for 255; *n_out = -1 when there are more, then hand the
+ * tan / cos grids over with tf_chan_set_param).  The caller evaluates tan and cos
+ * of those few values with ITS libm -- the one the reference's NumPy uses, which
+ * is what makes vol and d bit-identical -- and gives them back with
+ * tf_chan_set_angle_table (same order).  Saves two transcendental passes and two
+ * grid uploads per initialisation. */
+int tf_chan_set_angle(tf_handle h, const double* grid, double scalar, int is_grid_in_reference,
+                      double* distinct_out, int* n_out);
+int tf_chan_set_angle_table(tf_handle h, const double* tan_values, const double* cos_values, int n);
+
 /* Fix the run configuration and build the device layout.  Call after
  * tf_d8_build/tf_d8_set_codes and after all six tf_chan_set_param calls.
  * Replaces set_computed_input_vars (channels_base.py:726-752) and the rest of

@@ -43,6 +43,8 @@ SIGNATURES = {
     'tf_d8_get': (C.c_int, [handle_t, C.c_int, C.c_void_p]),
     'tf_d8_set_halo_dem': (C.c_int, [handle_t, _fp, _fp]),
     'tf_chan_set_param': (C.c_int, [handle_t, C.c_int, _dp, C.c_double, C.c_int]),
+    'tf_chan_set_angle': (C.c_int, [handle_t, _dp, C.c_double, C.c_int, _dp, C.POINTER(C.c_int)]),
+    'tf_chan_set_angle_table': (C.c_int, [handle_t, _dp, _dp, C.c_int]),
     'tf_chan_init': (C.c_int, [handle_t, C.c_int, C.c_int, C.c_double, _dp, _i32p, C.c_int,
                                C.c_int]),
     'tf_chan_set_rho': (C.c_int, [handle_t, C.c_double]),

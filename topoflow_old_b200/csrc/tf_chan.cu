@@ -16,21 +16,6 @@ static int chan_exchange_R(tf_handle h) {
 }
 
 // ---------------------------------------------------------------------------
-extern "C" int tf_chan_set_param(tf_handle h, int which, const double* grid, double scalar,
-                                 int is_grid_in_reference) {
-    TF_TRY(use_device(h));
-    TF_CHECK(which >= 0 && which < TF_P_COUNT, "tf_chan_set_param: unknown parameter %d", which);
-    HostParam& p = h->hp[which];
-    const size_t n = (size_t)h->g.nx * h->g.ny;
-    if (grid) p.grid.assign(grid, grid + n);
-    else { p.grid.clear(); p.grid.shrink_to_fit(); }
-    p.scalar = scalar;
-    p.is_grid = is_grid_in_reference != 0;
-    p.set = true;
-    h->chan_ready = false;
-    return 0;
-}
-
 extern "C" int tf_chan_set_rho(tf_handle h, double rho) {
     TF_CHECK(h != nullptr, "null handle");
     h->rho = rho;

@@ -101,7 +101,7 @@ struct PointSet {
 };
 
 struct HostParam {
-    std::vector<double> grid;   // dense ny*nx, empty when scalar
+    Raster<double> stage;       // the grid as it was handed over (device, float64); unset when scalar
     double scalar = 0.0;
     int is_grid = 0;            // grid-typed in the reference
     bool set = false;
@@ -134,6 +134,10 @@ struct tf_handle_s {
 
     // ---- routing ----------------------------------------------------------
     HostParam hp[TF_P_COUNT];
+    // bank angles handed over as angles (tf_chan_set_angle / tf_chan_set_angle_table)
+    std::vector<double> angle_values, angle_tan, angle_cos;
+    int angle_table_n = -1;               // > 0: the table is complete, aidx indexes it (+1)
+    bool angle_scalar = false, angle_is_grid = false;
     int wave = 0, law = 0, packed = 0;
     int mut_width = 0, mut_angle = 0;
     double dt = 0.0, rho = 1000.0;

@@ -154,6 +154,29 @@ class Strip(object):
             L.check(L.lib.tf_chan_set_param(self._h, int(which), L.ptr(g, C.c_double), 0.0,
                                             1 if is_grid is None else int(bool(is_grid))))
 
+    def set_angle(self, angle, is_grid=None):
+        """Hand over the bank angle [rad] (0-d or [ny, nx]); tan and cos are
+        evaluated here, with NumPy, for the distinct values only.  Returns False
+        when the grid holds more than 255 distinct angles (then use set_param
+        with TF_P_TAN_ANGLE / TF_P_COS_ANGLE grids)."""
+        distinct = np.zeros(255, dtype=np.float64)
+        n = C.c_int(-1)
+        if np.ndim(angle) == 0:
+            L.check(L.lib.tf_chan_set_angle(self._h, None, float(angle), int(bool(is_grid)),
+                                            L.ptr(distinct, C.c_double), C.byref(n)))
+        else:
+            g = _f64(angle)
+            assert g.shape == (self.ny, self.nx), g.shape
+            L.check(L.lib.tf_chan_set_angle(self._h, L.ptr(g, C.c_double), 0.0,
+                                            1 if is_grid is None else int(bool(is_grid)),
+                                            L.ptr(distinct, C.c_double), C.byref(n)))
+        if n.value < 0:
+            return False
+        a = np.ascontiguousarray(distinct[:n.value])
+        t, c = np.ascontiguousarray(np.tan(a)), np.ascontiguousarray(np.cos(a))
+        L.check(L.lib.tf_chan_set_angle_table(self._h, L.ptr(t, C.c_double), L.ptr(c, C.c_double), n.value))
+        return True
+
     def chan_init(self, wave, law, dt, da, outlets=(), allow_packed=True):
         da_rows = np.ascontiguousarray(np.broadcast_to(np.float64(da), (self.ny,)), dtype=np.float64)
         rc = np.ascontiguousarray(np.array(outlets, dtype=np.int32).reshape(-1, 2))

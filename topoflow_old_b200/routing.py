@@ -71,19 +71,26 @@ def setup_channels(strip, wave, law, dt, da, slope, width, angle, rough,
     if wave == L.KINEMATIC:
         slope = remove_bad_slopes(slope, report, reduce_min)    # :949-950
     d = np.zeros((ny, nx), dtype='float64')
-    d += d0                                                     # :903
-    tan_a, cos_a = np.tan(angle), np.cos(angle)
-    L2 = d * tan_a                                              # :957-960
-    A_wet = d * (width + L2)
-    vol = A_wet * ds
+    dry = np.ndim(d0) == 0 and float(d0) == 0.0
+    if dry:                                                     # the usual start: nothing to compute
+        A_wet = np.zeros((ny, nx), dtype='float64')
+        vol = np.zeros((ny, nx), dtype='float64')
+    else:
+        d += d0                                                 # :903
+        L2 = d * np.tan(angle)                                  # :957-960
+        A_wet = d * (width + L2)
+        vol = A_wet * ds
     strip.set_param(L.P_WIDTH, width, is_grid=np.ndim(width) > 0)
-    strip.set_param(L.P_TAN_ANGLE, tan_a, is_grid=np.ndim(angle) > 0)
-    strip.set_param(L.P_COS_ANGLE, cos_a, is_grid=np.ndim(angle) > 0)
+    # tan / cos with NumPy (the reference's libm), but only of the distinct angles
+    if not strip.set_angle(angle, is_grid=np.ndim(angle) > 0):
+        strip.set_param(L.P_TAN_ANGLE, np.tan(angle), is_grid=np.ndim(angle) > 0)
+        strip.set_param(L.P_COS_ANGLE, np.cos(angle), is_grid=np.ndim(angle) > 0)
     strip.set_param(L.P_SLOPE, slope, is_grid=True)
     strip.set_param(L.P_ROUGH, rough, is_grid=np.ndim(rough) > 0)
     strip.set_param(L.P_DS, np.float64(ds), is_grid=True)
     strip.chan_init(wave, law, dt, da, outlets=outlets, allow_packed=allow_packed)
-    strip.set_state(L.F_VOL, vol)
-    strip.set_state(L.F_D, d)
+    if not dry:                                                 # (tf_chan_init leaves vol = d = 0)
+        strip.set_state(L.F_VOL, vol)
+        strip.set_state(L.F_D, d)
     # u = 0, so the first Q = u * A_wet is 0 everywhere (:900, :1188)
     return dict(S_bed=slope, ds=ds, vol0=vol, d0=d, A_wet0=A_wet)
