@@ -425,6 +425,13 @@ int tf_comm_unique_id(uint8_t* id128);
  * single-process (docs/Peckham_2014_EMELI_FINAL.pdf). */
 int tf_comm_init(tf_handle h, int rank, int nranks, const uint8_t* id128);
 
+/* Which fields (enum tf_field, -1 terminated, fields_out3[3]) a strip exchanges
+ * with its neighbours in one time step of wave `wave`: point 0 = between the
+ * volume/depth phase and the velocity phase, point 1 = at the end of the step.
+ * The launch sequence of tf_chan_step reads the same table.  No counterpart in
+ * the reference (single process). */
+int tf_halo_plan(int wave, int point, int* fields_out3);
+
 /* Set the halo DEM rows by hand (single process tests): north/south float32
  * [nx] or NULL for "no neighbour" (global border). */
 int tf_d8_set_halo_dem(tf_handle h, const float* north_row,

@@ -66,5 +66,63 @@ def main():
         sys.stdout = stdout
 
 
+def big(n):
+    """The plane case blown up to n x n cells (same cfg files, a fractal DEM and
+    its D8 slopes written as RTG): per-update cost of the component with a 0-d
+    rain rate, with a constant rain GRID handed over before every update (what
+    EMELI does), and with update_until batching."""
+    from topoflow_old_b200.components import channels_kinematic_wave
+    from topoflow_old_b200.utils import synth
+    from oracle import d8 as od8      # noqa: F401  (only to keep the import surface of this script in one place)
+    gd = os.path.join(ROOT, 'tests', 'golden')
+    d = os.path.join(tempfile.mkdtemp(), 'plane_canal')
+    shutil.copytree(os.path.join(gd, 'plane_canal'), d)
+    rti = os.path.join(d, 'plane.rti')
+    txt = open(rti).read().replace('Number of columns:  20', 'Number of columns:  %d' % n)
+    txt = txt.replace('Number of rows:     20', 'Number of rows:     %d' % n)
+    open(rti, 'w').write(txt)
+    dem = synth.fractal_dem(n, n, seed=3, cell=10.0, roughness=8.0)
+    dem.astype('<f4').tofile(os.path.join(d, 'plane_DEM.rtg'))
+    np.full((n, n), 0.01, dtype='<f4').tofile(os.path.join(d, 'plane_slope.rtg'))
+    res = {}
+    for mode in ('scalar rain', 'constant rain grid', 'constant rain grid, update_until'):
+        comp = channels_kinematic_wave.channels_component()
+        stdout = sys.stdout
+        sys.stdout = open(os.devnull, 'w')
+        comp.initialize(cfg_file=os.path.join(d, 'Case1_channels_kinematic_wave.cfg'), SILENT=True)
+        sys.stdout = stdout
+        P = och.scalar(60.0 / 3.6e6) if mode == 'scalar rain' else np.full((n, n), 60.0 / 3.6e6)
+        for name in ('snowpack__melt_volume_flux', 'land_surface_water__baseflow_volume_flux',
+                     'glacier_ice__melt_volume_flux', 'land_surface_water__evaporation_volume_flux',
+                     'soil_surface_water__infiltration_volume_flux'):
+            comp.set_values(name, och.scalar(0))
+        for name in ('canals__count', 'sinks__count', 'sources__count'):
+            comp.set_values(name, np.array(0, dtype='int32'))
+        for k in 'QUDF':
+            setattr(comp, 'SAVE_%s_GRIDS' % k, False)
+            setattr(comp, 'SAVE_%s_PIXELS' % k, False)
+        steps = 200
+        comp.set_values('atmosphere_water__rainfall_volume_flux', P)
+        for _ in range(20):
+            comp.update(-1.0)
+        t = time.perf_counter()
+        if mode.endswith('update_until'):
+            comp.set_values('atmosphere_water__rainfall_volume_flux', P)
+            comp.update_until(float(comp.time) + steps * float(comp.dt))
+        else:
+            for _ in range(steps):
+                comp.set_values('atmosphere_water__rainfall_volume_flux', P)     # emeli.py:1841-1933
+                comp.update(-1.0)
+        res[mode] = (time.perf_counter() - t) / steps * 1e6
+        print('%dx%d  %-34s component.update() %9.1f us/step' % (n, n, mode, res[mode]), flush=True)
+        sys.stdout = open(os.devnull, 'w')
+        comp.finalize()
+        sys.stdout = stdout
+    print('constant rain grid / scalar rain = %.3f' % (res['constant rain grid'] / res['scalar rain']))
+
+
 if __name__ == '__main__':
-    main()
+    if len(sys.argv) > 2 and sys.argv[1] == 'big':
+        big(int(sys.argv[2]))
+    else:
+        main()

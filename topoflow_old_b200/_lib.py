@@ -82,6 +82,7 @@ SIGNATURES = {
     'tf_chan_assemble_R_dev': (C.c_int, [handle_t, _dp, _dp]),
     'tf_fill_pits': (C.c_int, [handle_t, _fp, C.c_float, _fp, _i64p, _i64p]),
     'tf_satzone_dzw': (C.c_int, [handle_t, _dp, _dp, C.c_double, _dp, C.c_double, _dp]),
+    'tf_halo_plan': (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_int)]),
     'tf_comm_unique_id': (C.c_int, [_u8p]),
     'tf_comm_init': (C.c_int, [handle_t, C.c_int, C.c_int, _u8p]),
 }

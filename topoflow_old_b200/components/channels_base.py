@@ -122,7 +122,7 @@ def _fingerprint(v):
     if a.ndim == 0:
         return ('s', float(a))
     flat = a.reshape(-1)
-    step = max(1, flat.size // 4096)
+    step = max(1, flat.size // 512)
     return (id(v), a.shape, flat[::step].tobytes(), flat[-1].tobytes())
 
 
@@ -471,7 +471,7 @@ class channels_component(BMI_base.BMI_component):
             # EMELI sets every flux into the component before every update
             # (emeli.py:1841-1933), changed or not.  A flux goes to the device
             # only when it IS a different array or its contents changed: the
-            # test is the array's identity plus a fingerprint of 4096 samples
+            # test is the array's identity plus a fingerprint of 512 samples
             # spread over the grid, which catches what providers do (they
             # rewrite whole grids) at a cost independent of the grid size.
             # TF_B200_ALWAYS_UPLOAD=1 restores the unconditional copy.

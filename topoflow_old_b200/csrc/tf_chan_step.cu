@@ -36,6 +36,34 @@ static int launch_phase_b(tf_handle h, cudaStream_t s, int y0, int y1) {
     return 0;
 }
 
+// ---- which rasters cross a strip boundary in one step of the tile kernels ----
+// One table for the launch sequence below and for tf_halo_plan (which
+// topoflow_old_b200/strips.py and the CPU strip test read): per wave, the
+// fields (enum tf_field) exchanged between the two phases and at the end of
+// the step, -1 terminated.
+static const int k_halo_plan[3][2][3] = {
+    /* kinematic */ {{-1, -1, -1}, {TF_F_QNEXT, -1, -1}},
+    /* diffusive */ {{TF_F_D, -1, -1}, {TF_F_QNEXT, -1, -1}},
+    /* dynamic   */ {{TF_F_D, -1, -1}, {TF_F_QNEXT, TF_F_U, -1}}};
+
+extern "C" int tf_halo_plan(int wave, int point, int* fields_out3) {
+    TF_CHECK(wave >= 0 && wave <= 2 && (point == 0 || point == 1) && fields_out3, "tf_halo_plan: bad argument");
+    for (int k = 0; k < 3; ++k) fields_out3[k] = k_halo_plan[wave][point][k];
+    return 0;
+}
+
+static int exchange_planned(tf_handle h, cudaStream_t s, int point) {
+    void* arr[3];
+    size_t es[3];
+    int n = 0;
+    for (int k = 0; k < 3 && k_halo_plan[h->wave][point][k] >= 0; ++k) {
+        const int f = k_halo_plan[h->wave][point][k];
+        arr[n] = (f == TF_F_D) ? (void*)h->d.p : ((f == TF_F_U) ? (void*)h->u.p : (void*)h->Qnext);
+        es[n++] = sizeof(double);
+    }
+    return n ? comm_exchange_rows(h, s, arr, es, n) : 0;
+}
+
 // ---- marching kernels (packed layout, tf_chan_march.cuh) ----------------------
 template <int WAVE, int LAW, bool RG>
 static int launch_march_t(tf_handle h, cudaStream_t s, int y0, int y1) {
@@ -180,11 +208,7 @@ static int queue_steps(tf_handle h, int n_steps, int record) {
         } else if (h->wave == TF_KINEMATIC) {
             if (!multi || g.ny < 32) {
                 TF_TRY(launch_kinematic(h, s, 0, g.ny));
-                if (multi) {
-                    void* arr[1] = {h->Qnext};
-                    size_t es[1] = {sizeof(double)};
-                    TF_TRY(comm_exchange_rows(h, s, arr, es, 1));
-                }
+                if (multi) TF_TRY(exchange_planned(h, s, 1));
             } else {
                 // edge bands first on the high-priority stream, their halo
                 // rows travel while the interior is computed
@@ -193,26 +217,16 @@ static int queue_steps(tf_handle h, int n_steps, int record) {
                 TF_CUDA(cudaStreamWaitEvent(e, h->ev_main, 0));
                 TF_TRY(launch_kinematic(h, e, 0, 8));
                 TF_TRY(launch_kinematic(h, e, g.ny - 8, g.ny));
-                void* arr[1] = {h->Qnext};
-                size_t es[1] = {sizeof(double)};
-                TF_TRY(comm_exchange_rows(h, e, arr, es, 1));
+                TF_TRY(exchange_planned(h, e, 1));
                 TF_CUDA(cudaEventRecord(h->ev_edge, e));
                 TF_TRY(launch_kinematic(h, s, 8, g.ny - 8));
                 TF_CUDA(cudaStreamWaitEvent(s, h->ev_edge, 0));
             }
         } else {
             TF_TRY(launch_phase_a(h, s, 0, g.ny));
-            if (multi) {
-                void* arr[1] = {h->d.p};
-                size_t es[1] = {sizeof(double)};
-                TF_TRY(comm_exchange_rows(h, s, arr, es, 1));
-            }
+            if (multi) TF_TRY(exchange_planned(h, s, 0));      // between the phases
             TF_TRY(launch_phase_b(h, s, 0, g.ny));
-            if (multi) {
-                void* arr[2] = {h->Qnext, h->u.p};
-                size_t es[2] = {sizeof(double), sizeof(double)};
-                TF_TRY(comm_exchange_rows(h, s, arr, es, h->wave == TF_DYNAMIC ? 2 : 1));
-            }
+            if (multi) TF_TRY(exchange_planned(h, s, 1));      // at the end of the step
         }
         if (record && h->n_outlets) {
             ChanArgs a = chan_args(h, 0, g.ny);

@@ -26,7 +26,9 @@ def neighbours(nranks, rank):
 
 
 def halo_plan(wave):
-    """Which rasters cross a strip boundary in one time step, in order.
+    """Which rasters cross a strip boundary in one time step, in order -- read
+    from the library's own table (tf_halo_plan), the one its launch sequence
+    follows:
 
     kinematic : the next step's Q (u * A_wet) once per step;
     diffusive : the new depth d between the two phases (the free-surface slope
@@ -34,10 +36,17 @@ def halo_plan(wave):
     dynamic   : d between the phases, then next Q and the new u (the momentum
                 flux reads the children's u and Q).
     Returns a list of (point_in_step, [raster names])."""
-    if wave == 'kinematic':
-        return [('end', ['Qnext'])]
-    if wave == 'diffusive':
-        return [('after_depth', ['d']), ('end', ['Qnext'])]
-    if wave == 'dynamic':
-        return [('after_depth', ['d']), ('end', ['Qnext', 'u'])]
-    raise ValueError(wave)
+    import ctypes as C
+    from . import _lib as L
+    waves = {'kinematic': L.KINEMATIC, 'diffusive': L.DIFFUSIVE, 'dynamic': L.DYNAMIC}
+    if wave not in waves:
+        raise ValueError(wave)
+    names = {L.F_D: 'd', L.F_QNEXT: 'Qnext', L.F_U: 'u'}
+    plan = []
+    for point, label in ((0, 'after_depth'), (1, 'end')):
+        buf = (C.c_int * 3)()
+        L.check(L.lib.tf_halo_plan(waves[wave], point, buf))
+        fields = [names[f] for f in buf if f >= 0]
+        if fields:
+            plan.append((label, fields))
+    return plan
