@@ -104,6 +104,14 @@ def build_strip(args, rank, nranks, device, unique_id=None, reduce_min=None, nx=
         s.comm_init(rank, nranks, unique_id)
     dx = np.full(ny, CELL, dtype=np.float32)
     dd = np.full(ny, np.float32(np.sqrt(np.float64(CELL) ** 2 * 2)), dtype=np.float32)
+    s.pits_filled = None
+    if getattr(args, 'fill_pits', False) and nranks == 1:
+        # the generator may fill the DEM's depressions first (not timed, not the default:
+        # the shipped cfgs run with FILL_PITS_IN_Z0 = 0); the fill is the library's own tf_fill_pits
+        t0 = time.time()
+        dem, n_raised, sweeps = s.fill_pits(dem)
+        s.pits_filled = {'cells_raised': n_raised, 'sweeps': sweeps, 'seconds': round(time.time() - t0, 2)}
+        log_('[rank %d] pit filling %.2fs %s' % (rank, time.time() - t0, s.pits_filled))
     t0 = time.time()
     stats = s.d8_build(dem, dx, dx, dd)
     log_('[rank %d] D8 build %.2fs %s' % (rank, time.time() - t0, stats))
@@ -637,8 +645,10 @@ def run_gpu(args):
             'config': {'workload': workload_text(args, D.world),
                        'grid_per_gpu': [int(s.ny), int(s.nx)], 'wave': args.wave,
                        'noflow_fraction': noflow,
-                       'pits': 'DEM not pit-filled (as FILL_PITS_IN_Z0 = 0 in the shipped cfgs): %d pits, each a '
-                               'no-flow sink' % int(s.d8_stats['n_pits']),
+                       'pits': ('DEM not pit-filled (as FILL_PITS_IN_Z0 = 0 in the shipped cfgs): %d pits, each a '
+                                'no-flow sink' % int(s.d8_stats['n_pits'])) if s.pits_filled is None else
+                               ('DEM pit-filled by tf_fill_pits %s: %d pits left (grid edge)' % (
+                                   json.dumps(s.pits_filled), int(s.d8_stats['n_pits']))),
                        'layout': 'generic-f64' if args.generic else 'packed (exact f32 params + angle table)',
                        'l2_policy': 'inputs larger than L2 (%.1f GB touched per step)' % (layout_bytes * cells / 1e9),
                        'parallelism': 'row strips x%d, halo rows over NCCL (%s)' % (
@@ -747,6 +757,7 @@ def main():
     ap.add_argument('--scaling', default='weak', choices=['weak', 'strong'],
                     help='weak: --size rows per GPU; strong: one --size x --size grid cut into N strips')
     ap.add_argument('--with-area', action='store_true', help='also compute (and time) the D8 contributing area')
+    ap.add_argument('--fill-pits', action='store_true', help='one GPU: fill the depressions of the DEM first')
     ap.add_argument('--coupled', action='store_true',
                     help='configs[4]: met + snow + evap + infil providers on the device + kinematic routing')
     ap.add_argument('--no-parity', action='store_true', help='skip the strips / single strip / oracle check')
