@@ -658,8 +658,8 @@ def run_gpu(args):
             'strong_scaling_dynamic': strong,
             'd8_area': None if area_s is None else {
                 'seconds': area_s, 'cells_per_s': total_cells / area_s if area_s else None,
-                'note': 'tf_d8_area, host call to host return; on strips every rank gathers the code grid '
-                        'and accumulates the whole grid (replicas, SURVEY 8e)'},
+                'note': 'tf_d8_area, host call to host return; on strips: owner computes, edge rows of the area '
+                        'exchanged until no flow path has anything left to hand over'},
             'e2e': {'value': e2e, 'unit': 'cell-updates/s', 'h2d_bytes_per_step': 8 * 6,
                     'd2h_bytes_per_step': 8 * 4 * s.n_outlets + 16},
             'e2e_grid_rain': None if e2e_grid is None else {

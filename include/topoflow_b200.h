@@ -150,11 +150,15 @@ int tf_d8_set_codes(tf_handle h, const uint8_t* codes, const float* dx,
  * (pixels.py:174-200); units_km != 0 divides by 1e6 first (A_units 'km^2').
  * n_unresolved_out (optional) counts flowing cells left at 0 (cycles).
  * On a strip with neighbours (tf_set_strip + tf_comm_init) the call is
- * collective: flow paths cross strips and the float32 sums must see the true
- * child values in the reference's order, so every rank gathers the code grid
- * of all strips over NCCL, accumulates the whole grid on its own GPU and keeps
- * its rows (da_rows is still this strip's [ny]); the global grid must have
- * fewer than 2^31 cells and fit one GPU (10 bytes per cell while it runs). */
+ * collective.  Flow paths cross strips and the float32 sums must see the true
+ * child values in the reference's order, so each strip accumulates what it
+ * can, the strips exchange the edge rows of the area grid, every cell whose
+ * last pending child lay in a neighbour's row is then computed and its flow
+ * path followed on, and so on until no strip has anything new: as many
+ * rounds as the most boundary crossings of one flow path, the same bits as
+ * one strip, any size of the global grid (da_rows is this strip's [ny]).  A
+ * periodic grid (flow wraps around the outer edges) instead gathers the code
+ * grid and accumulates the whole grid on every GPU (< 2^31 cells). */
 int tf_d8_area(tf_handle h, const double* da_rows, int units_km,
                int64_t* n_unresolved_out);
 

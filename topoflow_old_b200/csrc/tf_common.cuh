@@ -127,6 +127,7 @@ struct tf_handle_s {
     Raster<int32_t> pending;      // area: children still to finish
     float *dx = nullptr, *dy = nullptr, *dd = nullptr;   // per-row, float32
     bool have_d8 = false, have_area = false;
+    long long area_rounds = 0;            // strips: exchange rounds the last tf_d8_area took
     int lr_periodic = 0, tb_periodic = 0;
     float row0_len[3] = {0.f, 0.f, 0.f};  // dx, dy, dd of GLOBAL row 0 (tf_d8_set_row0_sizes)
     bool have_row0_len = false;

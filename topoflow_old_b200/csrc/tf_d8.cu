@@ -13,6 +13,8 @@
 //                   w1..w8 / p1..p8 index lists        (:719-835)
 //   k_area_*        contributing area by dependency counting (:1018-1261)
 // All integer/float32 results are bit-identical to the reference's.
+#include <stdlib.h>
+
 #include "tf_common.cuh"
 
 // neighbour k = 0..7 : UR, R, LR, B, LL, L, UL, T  (d8_global.py:381-385)
@@ -320,6 +322,104 @@ k_area_run(D8Args a, const uint8_t* __restrict__ code, const uint8_t* __restrict
         __threadfence();
         x = px; y = py; i = pi; c = pc;
         m = inmask[i];
+    }
+}
+
+// ---------------------------------------------------------------------------
+// The same on a strip with neighbours: a flow path may cross strip boundaries
+// any number of times, so the climb stops where the parent lies in a
+// neighbour's rows, and resumes there after the next exchange of the edge rows
+// of `area`.  A cell still sums its own value once, after all its children,
+// local or remote, in the reference's order: bit-identical to one strip.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float area_of_strip(const D8Args& a, int x, int y, unsigned m,
+                                               const float* area, float pa) {
+    float acc = pa;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int j = (k + 4) & 7;
+        if ((m >> j) & 1u)                                   // rows -1 and ny are the neighbours' edge rows
+            acc += __ldcg(&area[(int64_t)(y + c_dr[k]) * a.pitch + (x + c_dc[k])]);
+    }
+    return acc;
+}
+
+// compute cell (x, y), whose children are all final, and keep climbing while this
+// thread finishes the last child of the next parent and that parent is ours
+__device__ void area_climb(const D8Args& a, const uint8_t* __restrict__ code, const uint8_t* __restrict__ inmask,
+                           int32_t* pending, float* area, const double* __restrict__ da_rows, double unit_div,
+                           int x, int y) {
+    int64_t i = (int64_t)y * a.pitch + x;
+    int c = code[i];
+    unsigned m = inmask[i];
+    while (true) {
+        const float pa = (float)(da_rows[y] / unit_div);
+        area[i] = area_of_strip(a, x, y, m, area, pa);
+        const int k = __ffs(c) - 1;
+        const int px = x + c_dc[k], py = y + c_dr[k];
+        __threadfence();
+        if (py < 0 || py >= a.ny) return;                    // the neighbour strip goes on after the exchange
+        const int64_t pi = (int64_t)py * a.pitch + px;
+        const int pc = code[pi];
+        if (pc == 0) return;
+        const int old = atomicSub(&pending[pi], 1);
+        if (old != 1) return;
+        __threadfence();
+        x = px; y = py; i = pi; c = pc;
+        m = inmask[i];
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_area_run_strip(D8Args a, const uint8_t* __restrict__ code, const uint8_t* __restrict__ inmask,
+                 int32_t* pending, float* area, const double* __restrict__ da_rows, double unit_div) {
+    int x = blockIdx.x * blockDim.x + threadIdx.x;
+    int y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= a.nx || y >= a.ny) return;
+    const int64_t i = (int64_t)y * a.pitch + x;
+    if (code[i] == 0 || inmask[i] != 0) return;              // leaves start
+    area_climb(a, code, inmask, pending, area, da_rows, unit_div, x, y);
+}
+
+// After an exchange: every cell of the two edge rows looks at its children in the
+// neighbour's edge row; a child that has a value now and was not counted before
+// is counted (credited[side * pitch + x], one bit per direction), and the cell
+// that thereby loses its last pending child is computed and climbs on.
+__global__ void __launch_bounds__(256)
+k_area_resume(D8Args a, const uint8_t* __restrict__ code, const uint8_t* __restrict__ inmask,
+              int32_t* pending, float* area, const double* __restrict__ da_rows, double unit_div,
+              uint8_t* credited, unsigned long long* counters) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int side = blockIdx.y;                             // 0: row 0 (children in row -1), 1: row ny-1
+    if (x >= a.nx) return;
+    if ((side == 0 && !a.has_north) || (side == 1 && !a.has_south)) return;
+    const int y = side == 0 ? 0 : a.ny - 1;
+    if (side == 1 && a.ny == 1 && a.has_north) { /* a one-row strip is handled by side 0 and side 1 alike */ }
+    const int64_t i = (int64_t)y * a.pitch + x;
+    if (code[i] == 0) return;
+    const unsigned m = inmask[i];
+    unsigned cr = credited[side * a.pitch + x];
+    unsigned n_new = 0;
+    bool last = false;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int j = (k + 4) & 7;
+        const int yy = y + c_dr[k];
+        const bool remote = (side == 0) ? (yy == -1) : (yy == a.ny);
+        if (!remote || !((m >> j) & 1u) || ((cr >> j) & 1u)) continue;
+        if (__ldcg(&area[(int64_t)yy * a.pitch + (x + c_dc[k])]) > 0.0f) {
+            cr |= 1u << j;
+            ++n_new;
+            if (atomicSub(&pending[i], 1) == 1) last = true;
+        }
+    }
+    if (n_new) {
+        credited[side * a.pitch + x] = (uint8_t)cr;
+        atomicAdd(&counters[11], (unsigned long long)n_new);
+    }
+    if (last) {
+        __threadfence();
+        area_climb(a, code, inmask, pending, area, da_rows, unit_div, x, y);
     }
 }
 
@@ -642,6 +742,62 @@ static int area_replicated(tf_handle h, const double* d_da, int units_km, int64_
     return rc;
 }
 
+// Strips, owner computes: local climbs, then rounds of "exchange the edge rows of the
+// area, resume" until no strip credits a new remote child.  The number of rounds is the
+// largest number of strip boundaries one flow path crosses, plus one.
+static int area_strips(tf_handle h, const double* d_da, int units_km, int64_t* n_unresolved_out) {
+    const Geom& g = h->g;
+    TF_CHECK(h->nccl_comm != nullptr,
+             "tf_d8_area: this strip has neighbours but no communicator (tf_comm_init)");
+    TF_TRY(raster_alloc(h, h->area, 0));
+    TF_TRY(raster_alloc(h, h->pending, 0));
+    D8Args a = d8_args(h);
+    const double unit_div = units_km ? 1e6 : 1.0;
+    uint8_t* credited = nullptr;
+    TF_CUDA(cudaMalloc((void**)&credited, (size_t)2 * g.pitch));
+    int rc = 0;
+    long long rounds = 0;
+    do {
+        cudaMemsetAsync(credited, 0, (size_t)2 * g.pitch, h->stream);
+        cudaMemsetAsync(h->area.base, 0, sizeof(float) * (size_t)g.n_alloc, h->stream);
+        k_area_init<<<d8_grid(h), d8_block(), 0, h->stream>>>(a, h->code.p, h->inmask.p, h->pending.p, h->area.p);
+        k_area_run_strip<<<d8_grid(h), d8_block(), 0, h->stream>>>(a, h->code.p, h->inmask.p, h->pending.p,
+                                                                    h->area.p, d_da, unit_div);
+        if (cudaGetLastError() != cudaSuccess) { tf_set_error("tf_d8_area: launch failed"); rc = 1; break; }
+        while (true) {
+            ++rounds;
+            void* arr[1] = {h->area.p};
+            size_t es[1] = {sizeof(float)};
+            if ((rc = comm_exchange_rows(h, h->stream, arr, es, 1))) break;
+            cudaMemsetAsync(h->counters + 11, 0, sizeof(unsigned long long), h->stream);
+            k_area_resume<<<dim3((g.nx + 255) / 256, 2), 256, 0, h->stream>>>(a, h->code.p, h->inmask.p, h->pending.p,
+                                                                              h->area.p, d_da, unit_div, credited,
+                                                                              h->counters);
+            if ((rc = comm_allreduce_u64(h, h->stream, h->counters + 11, 1))) break;
+            unsigned long long n_new = 0;
+            if (cudaMemcpyAsync(&n_new, h->counters + 11, sizeof(n_new), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+                cudaStreamSynchronize(h->stream) != cudaSuccess) {
+                tf_set_error("tf_d8_area: %s", cudaGetErrorString(cudaGetLastError()));
+                rc = 1;
+                break;
+            }
+            if (n_new == 0) break;
+        }
+        if (rc) break;
+        cudaMemsetAsync(h->counters + 8, 0, sizeof(unsigned long long), h->stream);
+        k_area_count_unresolved<<<d8_grid(h), d8_block(), 0, h->stream>>>(a, h->code.p, h->area.p, h->counters);
+        if ((rc = comm_allreduce_u64(h, h->stream, h->counters + 8, 1))) break;
+        unsigned long long nbad = 0;
+        cudaMemcpyAsync(&nbad, h->counters + 8, sizeof(nbad), cudaMemcpyDeviceToHost, h->stream);
+        if (cudaStreamSynchronize(h->stream) != cudaSuccess) { tf_set_error("tf_d8_area: sync failed"); rc = 1; break; }
+        if (n_unresolved_out) *n_unresolved_out = (int64_t)nbad;
+        h->have_area = true;
+        h->area_rounds = rounds;
+    } while (0);
+    cudaFree(credited);
+    return rc;
+}
+
 extern "C" int tf_d8_area(tf_handle h, const double* da_rows, int units_km,
                           int64_t* n_unresolved_out) {
     TF_TRY(use_device(h));
@@ -651,8 +807,15 @@ extern "C" int tf_d8_area(tf_handle h, const double* da_rows, int units_km,
     double* d_da = nullptr;
     TF_CUDA(cudaMalloc((void**)&d_da, sizeof(double) * g.ny));
     TF_CUDA(cudaMemcpyAsync(d_da, da_rows, sizeof(double) * g.ny, cudaMemcpyHostToDevice, h->stream));
-    const int rc = (g.has_north || g.has_south) ? area_replicated(h, d_da, units_km, n_unresolved_out)
-                                                : area_whole_grid(h, d_da, units_km, n_unresolved_out);
+    // strips: owner computes (any size of the global grid); a periodic grid, whose flow paths wrap
+    // around the outer edges, still takes the replicated whole-grid route (TF_B200_AREA_REPLICATED=1
+    // forces it, for comparison)
+    const char* e = getenv("TF_B200_AREA_REPLICATED");
+    const bool strips = (g.has_north || g.has_south);
+    const bool replicate = strips && (h->lr_periodic || h->tb_periodic || (e && e[0] == '1'));
+    const int rc = !strips ? area_whole_grid(h, d_da, units_km, n_unresolved_out)
+                           : (replicate ? area_replicated(h, d_da, units_km, n_unresolved_out)
+                                        : area_strips(h, d_da, units_km, n_unresolved_out));
     cudaFree(d_da);
     return rc;
 }
