@@ -70,7 +70,8 @@ k_phase_b(const ChanArgs a) {
         // the dynamic wave needs the wetted perimeter itself (:166)
         const XSection xs = (WAVE == 1) ? chan_xsection_step(d[k], w[k], t[k], c[k], noflow)
                                         : chan_xsection(d[k], w[k], t[k], c[k], noflow);
-        double s_free = free_slope(a, i + k, code[k], d[k], S[k], ds[k]);
+        const double dpar = code[k] ? a.d[i + k + parent_offset(code[k], a.pitch)] : 0.0;
+        double s_free = free_slope_step(S[k], d[k], dpar, ds[k], WAVE == 2);
         double uu;
         if (WAVE == 1) {
             s_free = np_max0(s_free);                              // diffusive :118

@@ -528,7 +528,7 @@ k_march(const __grid_constant__ ChanArgs a) {
                         const double* row = (dr < 0) ? dnr[0] : ((dr > 0) ? dnr[2] : dnr[1]);
                         dpar = row[idx + dc];
                     }
-                    double s_free = Sv[k] + ((d - dpar) / ds);
+                    double s_free = free_slope_step(Sv[k], d, dpar, ds, WAVE == 2);
                     double uu;
                     XSection xs;
                     if (WAVE == 1) {

@@ -102,6 +102,9 @@ __device__ __forceinline__ XSection chan_xsection(double d, double w, double t, 
 #ifndef TF_RH_APPROX_DIV
 #define TF_RH_APPROX_DIV 1
 #endif
+#ifndef TF_FAST_MANNING
+#define TF_FAST_MANNING 1   /* Manning's division by n and the free-surface slope's by ds through div_approx */
+#endif
 #ifndef TF_FAST_SEED
 #define TF_FAST_SEED 1      /* cube-root seed from lg2.approx / ex2.approx instead of rcbrtf */
 #endif
@@ -157,11 +160,25 @@ __device__ __forceinline__ double pow_two_thirds(double x) {
     return c * c;
 }
 
+// S_free = S_bed + (d - d_parent) / ds (channels_base.py:1542-1543) inside the step kernels, where
+// it only feeds the velocity; get_values re-derives it with the exact division (k_derive)
+// (exact = true for the dynamic wave: its momentum balance amplifies last-bit differences)
+__device__ __forceinline__ double free_slope_step(double S_bed, double d, double d_parent, double ds, bool exact) {
+#if TF_FAST_MANNING
+    if (!exact) return S_bed + div_approx(d - d_parent, ds);
+#endif
+    return S_bed + ((d - d_parent) / ds);
+}
+
 // manning_formula :2561-2589 / law_of_the_wall :2593-2640
 template <int LAW>
 __device__ __forceinline__ double chan_velocity(double Rh, double S, double rough, double d) {
     if (LAW == 0) {
+#if TF_FAST_MANNING
+        return div_approx(pow_two_thirds(Rh) * sqrt(S), rough);    // (u only: within ~2 ulp of the quotient)
+#else
         return (pow_two_thirds(Rh) * sqrt(S)) / rough;
+#endif
     } else {
         double sm = (TF_AVAL / rough) * d;
         sm = np_maxv(sm, 1.1);
