@@ -43,8 +43,9 @@ def _run_strip(rank, world, uid, wave, out_dir):
     ones = np.ones(nr, dtype=np.float32)
     stats = s.d8_build(dem[r0:r0 + nr], 30 * ones, 30 * ones, np.float32(np.sqrt(1800.0)) * ones)
     code, ds = s.d8_get(L.D8_CODE), s.d8_get(L.D8_DS)
-    # contributing area: with strips every rank gathers the code grid, accumulates the whole
-    # grid on its own GPU and keeps its rows (rows of different size: a lat/lon-like da)
+    # contributing area: with strips each rank accumulates its rows and the edge rows of the area
+    # travel until no flow path has anything left to hand over (rows of different size: a
+    # lat/lon-like da)
     da_rows = 900.0 * (1.0 + 0.001 * np.arange(r0, r0 + nr))
     n_unres = s.d8_area(da_rows, units_km=True)
     area = s.d8_get(L.D8_AREA)
