@@ -457,6 +457,15 @@ def run_coupled(args):
     from topoflow_old_b200.coupled import CoupledRun
     D = Dist(args.gpus)
     args.wave = 'kinematic'
+    parity = None
+    if not args.no_parity:
+        parity = parity_leg(args, D)
+        ok = D.max(0.0 if (parity is None or parity['ok']) else 1.0) == 0.0
+        if not ok:
+            if D.rank == 0:
+                print(json.dumps({'error': 'parity check failed', 'parity': parity}), file=_OUT, flush=True)
+            D.close()
+            sys.exit(3)
     uid = Strip_uid(D)
     s = build_strip(args, D.rank, D.world, D.local_rank, uid,
                     reduce_min=(lambda v: -D.max(-v)) if D.world > 1 else None, keep_dem=True)
@@ -517,6 +526,7 @@ def run_coupled(args):
                          'note': 'step kernel bytes only (grid R + R1); the provider kernels of a 60 s round are '
                                  'inside ms_per_step but not in the byte count'},
             'volumes_m3': run.vol,
+            'parity': parity,
         }
     s.close()
     D.close()

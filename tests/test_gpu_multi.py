@@ -87,3 +87,73 @@ def test_two_gpu_strips_match_single_gpu(tmp_path, wave):
     assert parts[0]['n_unres'][0] == parts[1]['n_unres'][0] == one['n_unres'][0]
     assert one['Q'].max() > 0
     assert np.array_equal(parts[0]['stats'], one['stats'])       # all-reduced counters
+
+
+def _coupled_inputs():
+    from topoflow_old_b200.utils import synth
+    dem, w, a, n = _inputs()
+    u = lambda seed: synth.uniform_field(NX, NY, 0.0, 1.0, seed=seed, dtype=np.float64)
+    T_air = 6.0 - 12.0 * (np.float64(dem) - dem.min()) / (dem.max() - dem.min())
+    met = dict(dt=30.0, P=(200.0 / 3.6e6) * (0.5 + u(51)), T_air=T_air, T_surf=T_air - 1.0, Qn_SW=300.0,
+               Qn_LW=-50.0, rain_duration=100.0)
+    snow = dict(dt=12.0, c0=2.7, T0=-0.2, h0_snow=0.3 * u(52), h0_swe=0.1 * u(52), rho_snow=300.0)
+    evap = dict(dt=20.0, alpha=1.2, K_soil=0.45, soil_x=0.05, T_soil_x=0.0)
+    infil = dict(dt=6.0, Ks=7.2e-6 * (0.5 + u(53)), Ki=1e-7, qs=0.485, qi=0.375808, G=0.724)
+    return met, snow, evap, infil
+
+
+def _run_coupled_strip(rank, world, uid, out_dir):
+    """The coupled run of tests/test_gpu_coupled.py on strips: the providers work on their own
+    rows, only the "did every cell change" test of the interpolation is global."""
+    from topoflow_old_b200 import _lib as L
+    from topoflow_old_b200 import strips
+    from topoflow_old_b200.coupled import CoupledRun
+    from topoflow_old_b200.engine import Strip
+    from topoflow_old_b200.routing import setup_channels
+    dem, w, a, n = _inputs()
+    r0, nr = strips.strip_rows(NY, world, rank)
+    s = Strip(NX, nr, device=rank if world > 1 else 0)
+    if world > 1:
+        north, south = strips.neighbours(world, rank)
+        s.set_strip(r0, NY, north is not None, south is not None)
+        s.comm_init(rank, world, uid)
+    ones = np.ones(nr, dtype=np.float32)
+    s.d8_build(dem[r0:r0 + nr], 30 * ones, 30 * ones, np.float32(np.sqrt(1800.0)) * ones)
+    sl = lambda g: g[r0:r0 + nr].copy() if np.ndim(g) else g
+    slope = np.full((nr, NX), 0.01) + 0.001 * np.float64(sl(n))
+    setup_channels(s, L.KINEMATIC, L.MANNING, 2.0, 900.0, slope, sl(w), sl(a), sl(n),
+                   outlets=[(nr // 2, NX // 2)], ds=s.d8_get(L.D8_DS))
+    met, snow, evap, infil = [{k: sl(v) for k, v in d.items()} for d in _coupled_inputs()]
+    run = CoupledRun(s, 2.0, met, snow, evap, infil)
+    run.run_until(120.0)
+    assert run.bad[0] == -1 and run.bad[1] == -1
+    out = dict(vol=s.get(L.F_VOL), d=s.get(L.F_D), u=s.get(L.F_U), Q=s.get(L.F_Q), SM=run.get(run.SM.obj),
+               ET=run.get(run.ET.obj), IN=run.get(run.IN.obj), I=run.get(run.I),
+               lin=np.array([run.SM.linear, run.ET.linear, run.IN.linear]),
+               vols=np.array([run.vol[k] for k in ('SM', 'ET', 'IN', 'R')]))
+    np.savez(os.path.join(out_dir, 'c%d_r%d.npz' % (world, rank)), **out)
+    s.close()
+
+
+def _coupled_worker(rank, world, uid, out_dir):
+    _run_coupled_strip(rank, world, uid, out_dir)
+
+
+def test_two_gpu_coupled_run_matches_single_gpu(tmp_path):
+    if _n_devices() < 2:
+        pytest.skip('needs 2 GPUs')
+    import torch.multiprocessing as mp
+    from topoflow_old_b200.engine import Strip
+    uid = Strip.comm_unique_id()
+    mp.spawn(_coupled_worker, args=(2, uid, str(tmp_path)), nprocs=2, join=True)
+    _run_coupled_strip(0, 1, None, str(tmp_path))
+    one = np.load(str(tmp_path / 'c1_r0.npz'))
+    parts = [np.load(str(tmp_path / ('c2_r%d.npz' % r))) for r in range(2)]
+    for key in ('vol', 'd', 'u', 'Q', 'SM', 'ET', 'IN', 'I'):
+        got = np.concatenate([p[key] for p in parts], axis=0)
+        assert np.array_equal(got, one[key]), key
+    for p in parts:
+        assert np.array_equal(p['lin'], one['lin'])              # the same interpolation decisions
+    vols = parts[0]['vols'] + parts[1]['vols']
+    assert np.allclose(vols, one['vols'], rtol=1e-11, atol=0)
+    assert one['Q'].max() > 0
