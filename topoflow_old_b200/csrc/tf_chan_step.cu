@@ -251,16 +251,29 @@ extern "C" int tf_chan_step(tf_handle h, int n_steps, double* taps_out, double* 
     TF_TRY(use_device(h));
     TF_TRY(queue_steps(h, n_steps, taps_out != nullptr || canals_in_out != nullptr));
     cudaStream_t s = h->stream;
-    if (taps_out && h->n_outlets && n_steps)
-        TF_CUDA(cudaMemcpyAsync(taps_out, h->taps, sizeof(double) * (size_t)n_steps * h->n_outlets * 4,
-                                cudaMemcpyDeviceToHost, s));
+    // Everything that comes back lands in one page-locked staging block first: copies into the
+    // caller's pageable arrays would each be staged by the driver with a wait of its own; this
+    // way the three copies are queued behind the kernels and the call waits once.
+    const size_t n_taps = (taps_out && h->n_outlets && n_steps) ? (size_t)n_steps * h->n_outlets * 4 : 0;
     const int nc = h->pts[TF_PT_CANALS_IN].n;
-    if (canals_in_out && nc && n_steps)
-        TF_CUDA(cudaMemcpyAsync(canals_in_out, h->canal_taps, sizeof(double) * (size_t)n_steps * nc,
-                                cudaMemcpyDeviceToHost, s));
-    long long bad[2] = {0, 0};
-    TF_CUDA(cudaMemcpyAsync(bad, h->bad, sizeof(bad), cudaMemcpyDeviceToHost, s));
+    const size_t n_can = (canals_in_out && nc && n_steps) ? (size_t)n_steps * nc : 0;
+    const size_t need = sizeof(double) * (n_taps + n_can) + 2 * sizeof(long long);
+    if (need > h->back_cap) {
+        if (h->back) cudaFreeHost(h->back);
+        h->back = nullptr; h->back_cap = 0;
+        const size_t cap = need < 65536 ? 65536 : need;
+        TF_CUDA(cudaHostAlloc((void**)&h->back, cap, cudaHostAllocDefault));
+        h->back_cap = cap;
+    }
+    long long* bad = reinterpret_cast<long long*>(h->back);
+    double* b_taps = reinterpret_cast<double*>(h->back + 2 * sizeof(long long));
+    double* b_can = b_taps + n_taps;
+    if (n_taps) TF_CUDA(cudaMemcpyAsync(b_taps, h->taps, sizeof(double) * n_taps, cudaMemcpyDeviceToHost, s));
+    if (n_can) TF_CUDA(cudaMemcpyAsync(b_can, h->canal_taps, sizeof(double) * n_can, cudaMemcpyDeviceToHost, s));
+    TF_CUDA(cudaMemcpyAsync(bad, h->bad, 2 * sizeof(long long), cudaMemcpyDeviceToHost, s));
     TF_CUDA(cudaStreamSynchronize(s));
+    if (n_taps) memcpy(taps_out, b_taps, sizeof(double) * n_taps);
+    if (n_can) memcpy(canals_in_out, b_can, sizeof(double) * n_can);
     if (bad_out) {
         const long long none = 0x7fffffffffffffffLL;
         bad_out[0] = bad[0] == none ? -1 : bad[0];
@@ -401,6 +414,8 @@ int chan_free(tf_handle h) {
         if (h->pts[k].val) cudaFree(h->pts[k].val);
         h->pts[k] = PointSet();
     }
+    if (h->back) cudaFreeHost(h->back);
+    h->back = nullptr; h->back_cap = 0;
     h->chan_ready = false;
     return 0;
 }

@@ -186,6 +186,8 @@ struct tf_handle_s {
     double* canal_taps = nullptr;         // device [cap][n_canals]
     int taps_cap = 0;
     long long* bad = nullptr;             // device [2]
+    char* back = nullptr;                 // page-locked staging of what tf_chan_step copies back
+    size_t back_cap = 0;
     double* partial = nullptr;            // device scratch for reductions
     int partial_cap = 0;
     double* scratch64 = nullptr;          // one raster for derived fields
