@@ -34,6 +34,14 @@
 #ifndef TF_LEAN_CHECKS
 #define TF_LEAN_CHECKS 1
 #endif
+#ifndef TF_GRID_CONSTANT
+#define TF_GRID_CONSTANT 0
+#endif
+#if TF_GRID_CONSTANT
+#define TF_GC __grid_constant__
+#else
+#define TF_GC
+#endif
 #ifndef TF_TILE_RCP
 #define TF_TILE_RCP 1   /* depth divisions through precomputed reciprocals (exact, div_by_rcp) */
 #endif
@@ -330,7 +338,7 @@ __device__ __forceinline__ void store_mstate(const ChanArgs& a, int64_t i, const
 // regrouping moves u by at most 1 ulp, next to the ~2 ulp of the cube root.
 template <bool PACKED, int LAW, bool KF>
 __global__ void __launch_bounds__(256, TF_MINBLOCKS)
-k_step_kinematic(const ChanArgs a) {
+k_step_kinematic(const TF_GC ChanArgs a) {
     const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
     const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
     if (x4 >= a.pitch || y >= a.y_end) return;
@@ -404,7 +412,7 @@ k_step_kinematic(const ChanArgs a) {
 // ---------------------------------------------------------------------------
 template <bool PACKED>
 __global__ void __launch_bounds__(256, TF_MINBLOCKS_AB)
-k_phase_a(const ChanArgs a) {
+k_phase_a(const TF_GC ChanArgs a) {
     const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
     const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
     if (x4 >= a.pitch || y >= a.y_end) return;

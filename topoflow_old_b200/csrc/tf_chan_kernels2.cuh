@@ -27,7 +27,7 @@ __device__ __forceinline__ double free_slope(const ChanArgs& a, int64_t idx, int
 // SM at 64 registers without spills measured 3 % faster than 5 at 48 with)
 template <bool PACKED, int LAW, int WAVE>
 __global__ void __launch_bounds__(256, (WAVE == 2) ? TF_MINBLOCKS_AB - 1 : TF_MINBLOCKS_AB)
-k_phase_b(const ChanArgs a) {
+k_phase_b(const TF_GC ChanArgs a) {
     const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
     const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
     if (x4 >= a.pitch || y >= a.y_end) return;
