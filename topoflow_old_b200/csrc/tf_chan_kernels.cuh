@@ -34,6 +34,10 @@
 #ifndef TF_LEAN_CHECKS
 #define TF_LEAN_CHECKS 1
 #endif
+#ifndef TF_Q_SMEM
+#define TF_Q_SMEM 0      /* 1: the tile's discharge (+ a one-cell ring) staged in shared memory for the inflow gather */
+#endif
+#define TF_SQW 68
 #ifndef TF_GRID_CONSTANT
 #define TF_GRID_CONSTANT 0
 #endif
@@ -228,7 +232,7 @@ __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int 
                                                  double (&Q)[CPT], double (&v)[CPT], double (&d)[CPT],
                                                  double (&w)[CPT], double (&t)[CPT], double (&c)[CPT],
                                                  double (&ds)[CPT], double (&dwv)[CPT], int (&code)[CPT],
-                                                 int (&m)[CPT], int (&ms)[CPT]) {
+                                                 int (&m)[CPT], int (&ms)[CPT], const double* sqc = nullptr) {
     int mask[CPT];
     ld4(a.Q + i, Q);
     ld4c(a.vol + i, v);
@@ -265,7 +269,20 @@ __device__ __forceinline__ void volume_and_depth(const ChanArgs& a, int x4, int 
         apply_overbank(a, m[k], dwv[k], w[k], t[k], c[k]);
         double acc = v[k] + (R[k] * da) * dt;                  // :1334
         int mk = mask[k];
-#if TF_GATHER_UNROLL
+#if TF_Q_SMEM
+        {
+            // the same eight adds, the children's discharge read from the block's shared tile
+            const double* q = sqc + k;
+            if (mk & 1) acc += dt * q[TF_SQW - 1];
+            if (mk & 2) acc += dt * q[-1];
+            if (mk & 4) acc += dt * q[-TF_SQW - 1];
+            if (mk & 8) acc += dt * q[-TF_SQW];
+            if (mk & 16) acc += dt * q[-TF_SQW + 1];
+            if (mk & 32) acc += dt * q[1];
+            if (mk & 64) acc += dt * q[TF_SQW + 1];
+            if (mk & 128) acc += dt * q[TF_SQW];
+        }
+#elif TF_GATHER_UNROLL
         // the k = 1..8 adds of :1346-1361 in order, each predicated on its bit
         // of the mask; offsets are compile-time forms of the pitch, and the
         // east / west child of a cell pair is already in registers
@@ -328,6 +345,36 @@ __device__ __forceinline__ void store_mstate(const ChanArgs& a, int64_t i, const
     if (changed) st4(a.mstate + i, nw);
 }
 
+#if TF_Q_SMEM
+// Stage rows y0-1 .. y0+8, columns x0-1 .. x0+64 of Q in shared memory; returns the pointer to
+// this thread's first cell in the tile.  Every thread of the block must call it (barrier).
+__device__ __forceinline__ const double* stage_Q_tile(const ChanArgs& a, double (*sq)[TF_SQW], int x4, int y) {
+    const int r = threadIdx.y, lane = threadIdx.x;
+    const double* Q = a.Q;
+    if (y <= a.ny) {                                        // (row ny is an apron row: valid memory)
+        const int64_t i = (int64_t)y * a.pitch + x4;
+        const double2 q = *reinterpret_cast<const double2*>(Q + i);
+        sq[r + 1][1 + 2 * lane] = q.x; sq[r + 1][2 + 2 * lane] = q.y;
+        if (lane == 0) sq[r + 1][0] = Q[i - 1];
+        if (lane == 31) sq[r + 1][65] = Q[i + 2];
+        if (r == 0) {
+            const double2 n = *reinterpret_cast<const double2*>(Q + i - a.pitch);
+            sq[0][1 + 2 * lane] = n.x; sq[0][2 + 2 * lane] = n.y;
+            if (lane == 0) sq[0][0] = Q[i - a.pitch - 1];
+            if (lane == 31) sq[0][65] = Q[i - a.pitch + 2];
+        }
+        if (r == 7 || y == a.ny) {
+            const double2 n = *reinterpret_cast<const double2*>(Q + i + a.pitch);
+            sq[r + 2][1 + 2 * lane] = n.x; sq[r + 2][2 + 2 * lane] = n.y;
+            if (lane == 0) sq[r + 2][0] = Q[i + a.pitch - 1];
+            if (lane == 31) sq[r + 2][65] = Q[i + a.pitch + 2];
+        }
+    }
+    __syncthreads();
+    return &sq[r + 1][1 + 2 * lane];
+}
+#endif
+
 // ---------------------------------------------------------------------------
 // kinematic wave: the whole step in one pass
 // ---------------------------------------------------------------------------
@@ -341,6 +388,12 @@ __global__ void __launch_bounds__(256, TF_MINBLOCKS)
 k_step_kinematic(const TF_GC ChanArgs a) {
     const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
     const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
+#if TF_Q_SMEM
+    __shared__ double sq[10][TF_SQW];
+    const double* sqc = stage_Q_tile(a, sq, x4, y);
+#else
+    const double* sqc = nullptr;
+#endif
     if (x4 >= a.pitch || y >= a.y_end) return;
     const int64_t i = (int64_t)y * a.pitch + x4;
     double Q[CPT], v[CPT], d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT], S[CPT], n[CPT], u[CPT], Qn[CPT];
@@ -363,7 +416,7 @@ k_step_kinematic(const TF_GC ChanArgs a) {
         else prefetch_slope_rough<PACKED>(a, j);
     }
 #endif
-    volume_and_depth<PACKED, false>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
+    volume_and_depth<PACKED, false>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms, sqc);
     if (KF) ld4(a.kfac + i, S);
     else load_slope_rough<PACKED>(a, i, S, n);
     bool bad_d = false, bad_u = false;
@@ -415,6 +468,12 @@ __global__ void __launch_bounds__(256, TF_MINBLOCKS_AB)
 k_phase_a(const TF_GC ChanArgs a) {
     const int x4 = (blockIdx.x * 32 + threadIdx.x) * CPT;
     const int y = a.y_begin + blockIdx.y * 8 + threadIdx.y;
+#if TF_Q_SMEM
+    __shared__ double sq[10][TF_SQW];
+    const double* sqc = stage_Q_tile(a, sq, x4, y);
+#else
+    const double* sqc = nullptr;
+#endif
     if (x4 >= a.pitch || y >= a.y_end) return;
     const int64_t i = (int64_t)y * a.pitch + x4;
     double Q[CPT], v[CPT], d[CPT], w[CPT], t[CPT], c[CPT], ds[CPT], dwv[CPT];
@@ -423,7 +482,7 @@ k_phase_a(const TF_GC ChanArgs a) {
     if (a.pf_rows > 0 && y + a.pf_rows < a.y_end)
         prefetch_ahead_a<PACKED>(a, i + (int64_t)a.pf_rows * a.pitch);
 #endif
-    volume_and_depth<PACKED, true>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms);
+    volume_and_depth<PACKED, true>(a, x4, y, i, Q, v, d, w, t, c, ds, dwv, code, m, ms, sqc);
     st4(a.vol + i, v);
     st4(a.d + i, d);
     store_mstate(a, i, ms, m, d, w, t, dwv);
