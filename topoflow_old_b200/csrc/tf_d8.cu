@@ -394,7 +394,7 @@ k_area_resume(D8Args a, const uint8_t* __restrict__ code, const uint8_t* __restr
     if (x >= a.nx) return;
     if ((side == 0 && !a.has_north) || (side == 1 && !a.has_south)) return;
     const int y = side == 0 ? 0 : a.ny - 1;
-    if (side == 1 && a.ny == 1 && a.has_north) { /* a one-row strip is handled by side 0 and side 1 alike */ }
+    // (a one-row strip: both sides look at the same cell, each at its own remote children)
     const int64_t i = (int64_t)y * a.pitch + x;
     if (code[i] == 0) return;
     const unsigned m = inmask[i];
