@@ -16,7 +16,7 @@ void tf_set_error(const char* fmt, ...) {
 extern "C" const char* tf_last_error(void) { return g_err; }
 
 extern "C" const char* tf_version(void) {
-    return "topoflow_b200 0.1 (sm_100a, CUDA " TF_STR(CUDART_VERSION) ")";
+    return "topoflow_b200 0.2 (sm_100a, CUDA " TF_STR(CUDART_VERSION) ")";
 }
 
 extern "C" int tf_device_count(void) {
