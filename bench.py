@@ -130,7 +130,7 @@ def build_strip(args, rank, nranks, device, unique_id=None, reduce_min=None, nx=
     t0 = time.time()
     if want_area:
         t1 = time.time()
-        s.d8_area(CELL * CELL, units_km=True)
+        s.area_unresolved = s.d8_area(CELL * CELL, units_km=True)
         s.area_seconds = time.time() - t1
     s.noflow_fraction = float((code == 0).mean())
     setup_channels(s, WAVE_ID[wave], L.MANNING, DT[wave], CELL * CELL, np.float64(slope),
@@ -668,6 +668,8 @@ def run_gpu(args):
             'strong_scaling_dynamic': strong,
             'd8_area': None if area_s is None else {
                 'seconds': area_s, 'cells_per_s': total_cells / area_s if area_s else None,
+                'exchange_rounds': getattr(s, 'area_rounds', 0), 'unresolved_cells': int(s.area_unresolved),
+                'global_cells': int(total_cells),
                 'note': 'tf_d8_area, host call to host return; on strips: owner computes, edge rows of the area '
                         'exchanged until no flow path has anything left to hand over'},
             'e2e': {'value': e2e, 'unit': 'cell-updates/s', 'h2d_bytes_per_step': 8 * 6,

@@ -162,6 +162,10 @@ int tf_d8_set_codes(tf_handle h, const uint8_t* codes, const float* dx,
 int tf_d8_area(tf_handle h, const double* da_rows, int units_km,
                int64_t* n_unresolved_out);
 
+/* Strips: how many exchange rounds the last tf_d8_area took (0 for a single
+ * strip or the replicated route).  No counterpart in the reference. */
+long long tf_d8_area_rounds(tf_handle h);
+
 /* Copy one D8 product to a dense host grid of the field's element type: the
  * attributes other components read from the embedded d8 object (d8_grid,
  * parent_ID_grid, ds, dw, A; d8_base.py:119-123, channels_base.py:756-793). */

@@ -40,6 +40,7 @@ SIGNATURES = {
     'tf_d8_set_row0_sizes': (C.c_int, [handle_t, C.c_float, C.c_float, C.c_float]),
     'tf_d8_set_codes': (C.c_int, [handle_t, _u8p, _fp, _fp, _fp, C.c_int, C.c_int]),
     'tf_d8_area': (C.c_int, [handle_t, _dp, C.c_int, _i64p]),
+    'tf_d8_area_rounds': (C.c_longlong, [handle_t]),
     'tf_d8_get': (C.c_int, [handle_t, C.c_int, C.c_void_p]),
     'tf_d8_set_halo_dem': (C.c_int, [handle_t, _fp, _fp]),
     'tf_chan_set_param': (C.c_int, [handle_t, C.c_int, _dp, C.c_double, C.c_int]),

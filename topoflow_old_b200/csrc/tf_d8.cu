@@ -820,6 +820,8 @@ extern "C" int tf_d8_area(tf_handle h, const double* da_rows, int units_km,
     return rc;
 }
 
+extern "C" long long tf_d8_area_rounds(tf_handle h) { return h ? h->area_rounds : -1; }
+
 extern "C" int tf_d8_get(tf_handle h, int which, void* host_out) {
     TF_TRY(use_device(h));
     TF_CHECK(host_out != nullptr, "tf_d8_get: host_out is NULL");

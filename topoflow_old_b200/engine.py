@@ -108,6 +108,7 @@ class Strip(object):
         n_bad = C.c_int64(0)
         L.check(L.lib.tf_d8_area(self._h, L.ptr(da_rows, C.c_double), int(bool(units_km)),
                                  C.byref(n_bad)))
+        self.area_rounds = int(L.lib.tf_d8_area_rounds(self._h))
         return int(n_bad.value)
 
     def d8_get(self, which):
