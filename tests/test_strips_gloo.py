@@ -137,3 +137,103 @@ def test_two_strips_equal_one_grid(tmp_path, wave_name):
     assert ch.Q.max() > 0
     for k, name in enumerate(('vol', 'd', 'u')):
         assert np.array_equal(got[k], getattr(ch, name)), name
+
+
+# ---------------------------------------------------------------------------
+# contributing area on strips: the owner-computes rounds of csrc/tf_d8.cu
+# (area_strips), restated in NumPy and run by two gloo processes
+# ---------------------------------------------------------------------------
+def _area_worker(rank, world, port, out_dir):
+    import torch
+    import torch.distributed as dist
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    case = make_case(40, 36, seed=31)
+    code = case['d8']['d8_grid']
+    ny, nx = code.shape
+    r0, n = strips.strip_rows(ny, world, rank)
+    north, south = strips.neighbours(world, rank)
+    pa = np.float32(np.float64(case['da']) / 1e6)
+    # local rows 1..n are owned, row 0 and row n+1 are the neighbours' edge rows
+    C = np.zeros((n + 2, nx), dtype=np.uint8)
+    C[1:n + 1] = code[r0:r0 + n]
+    if north is not None:
+        C[0] = code[r0 - 1]
+    if south is not None:
+        C[n + 1] = code[r0 + n]
+    A = np.zeros((n + 2, nx), dtype=np.float32)
+    kcode = {c: k for k, c in enumerate(od8.CODE_LIST)}
+
+    def children(y, x):
+        """(k, yy, xx) of the neighbours that drain into (y, x), in the reference's order k = 0..7."""
+        out = []
+        for k, (dr, dc) in enumerate(od8.NBR):
+            yy, xx = y + dr, x + dc
+            if 0 <= yy < n + 2 and 0 <= xx < nx and C[yy, xx] == od8.CODE_LIST[(k + 4) % 8]:
+                out.append((k, yy, xx))
+        return out
+
+    pending = {(y, x): len(children(y, x)) for y in range(1, n + 1) for x in range(nx) if C[y, x]}
+    credited = set()
+
+    def climb(y, x):
+        while True:
+            acc = np.float32(pa)
+            for _, yy, xx in children(y, x):
+                acc = np.float32(acc + A[yy, xx])
+            A[y, x] = acc
+            dr, dc = od8.NBR[kcode[int(C[y, x])]]
+            py, px = y + dr, x + dc
+            if not (1 <= py <= n) or not (0 <= px < nx) or C[py, px] == 0:
+                return                                   # the neighbour strip (or nobody) goes on
+            pending[(py, px)] -= 1
+            if pending[(py, px)]:
+                return
+            y, x = py, px
+
+    for (y, x), p in list(pending.items()):
+        if p == 0:
+            climb(y, x)
+    rounds = 0
+    while True:
+        rounds += 1
+        for peer, mine, theirs in ((north, 1, 0), (south, n, n + 1)):
+            if peer is None:
+                continue
+            req = dist.isend(torch.from_numpy(A[mine].copy()), peer)
+            buf = torch.empty(nx, dtype=torch.float32)
+            dist.recv(buf, peer)
+            req.wait()
+            A[theirs] = buf.numpy()
+        n_new = 0
+        for y, edge in ((1, 0), (n, n + 1)):
+            for x in range(nx):
+                if not C[y, x]:
+                    continue
+                for k, yy, xx in children(y, x):
+                    if yy == edge and A[yy, xx] > 0 and (y, x, k) not in credited:
+                        credited.add((y, x, k))
+                        n_new += 1
+                        pending[(y, x)] -= 1
+                        if pending[(y, x)] == 0:
+                            climb(y, x)
+        t = torch.tensor([n_new])
+        dist.all_reduce(t)
+        if int(t.item()) == 0:
+            break
+    np.save(os.path.join(out_dir, 'area_%d.npy' % rank), A[1:n + 1])
+    np.save(os.path.join(out_dir, 'rounds_%d.npy' % rank), np.array([rounds]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_area_rounds_on_two_strips_equal_one_grid(tmp_path):
+    import torch.multiprocessing as mp
+    world = 2
+    mp.spawn(_area_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    case = make_case(40, 36, seed=31)
+    want = od8.area_grid_fast(case['d8']['d8_grid'], case['da'], 'km^2')
+    got = np.concatenate([np.load(str(tmp_path / ('area_%d.npy' % r))) for r in range(world)], axis=0)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert int(np.load(str(tmp_path / 'rounds_0.npy'))[0]) >= 2      # at least one flow path crossed the cut
